@@ -1,0 +1,119 @@
+/* b200msm -- C ABI of the B200-native multi-scalar-multiplication engine.
+ *
+ * This is the drop-in boundary for the MSM hot path of clearmatics/libff.  libff has no runtime
+ * plugin interface; the path's extension point is the compile-time dispatch
+ *   libff::multi_exp<G, Fr, Method, Form>()                 multiexp.tcc:643-688 (decl multiexp.hpp:63-73)
+ *     -> internal::multi_exp_implementation<...>::multi_exp_inner   multiexp.tcc:198-212, 276-381, 507-633
+ *   libff::batch_exp<G, Fr>()                               multiexp.tcc:875-915 (windowed_exp :848-873)
+ *   libff::batch_to_special<G>()                            multiexp.tcc:949-974
+ * (paths relative to libff/algebra/scalar_multiplication/).  The header
+ * libff_b200/include/libff_b200.hpp specialises exactly those templates and forwards to the
+ * functions below, so existing call sites stay source-identical.
+ *
+ * Conventions follow libff's own C ABI (ffi/ffi.h:13-95, ffi/ffi.cpp:16-54,124-260): every
+ * function returns `bool` (false on any size mismatch, invalid argument or CUDA error), buffers
+ * are caller-owned (pointer, byte-size) pairs whose sizes must match exactly, outputs are written
+ * only on success, nothing throws across the boundary.  In addition the last failure's text is
+ * kept per thread (b200msm_last_error).
+ *
+ * Unlike ffi.h (big-endian plain values), these entry points take libff's IN-MEMORY layout so
+ * that `&*vec.begin()` can be passed with no host-side conversion:
+ *   field element  = Fp_model::mont_repr: little-endian 64-bit limbs, Montgomery form
+ *                    (fields/bigint.hpp:28-65, fields/fp.hpp:43)
+ *   group element  = X | Y | Z coordinates, contiguous, stride sizeof(GroupT)
+ *                    (alt_bn128_g1.hpp:44-46, alt_bn128_g2.hpp:45, bls12_377_g1.hpp:44,
+ *                     bw6_761_g1.hpp:37-39): Jacobian, bw6_761 homogeneous projective
+ *   scalar         = Fr element in Montgomery form (what std::vector<Fr> holds)
+ * Returned points are valid representatives in the reference's coordinate system; they compare
+ * equal (operator==) to libff's result and have bit-identical affine coordinates.
+ *
+ * There is no CPU fallback: every entry point fails with an error if no CUDA device is usable.
+ */
+#ifndef B200MSM_H
+#define B200MSM_H
+
+#include <stdbool.h>
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* group ids */
+#define B200MSM_ALT_BN128_G1 0u /* 96 B elements, 32 B scalars  */
+#define B200MSM_ALT_BN128_G2 1u /* 192 B elements, 32 B scalars */
+#define B200MSM_BLS12_377_G1 2u /* 144 B elements, 32 B scalars */
+#define B200MSM_BW6_761_G1 3u   /* 288 B elements, 48 B scalars */
+#define B200MSM_NUM_GROUPS 4u
+
+/* multi_exp_base_form (multiexp.hpp:49-58) */
+#define B200MSM_FORM_NORMAL 0u  /* arbitrary Z */
+#define B200MSM_FORM_SPECIAL 1u /* Z = 1, or the zero element */
+
+/* Binds the calling process to CUDA device `device` (>= 0) and creates its stream and scratch
+ * pool; idempotent for the same device.  Mirrors <curve>_init() (ffi/ffi.cpp:124-128,194-198):
+ * call once before anything else, not thread-safe. */
+bool b200msm_init(int device);
+void b200msm_shutdown(void);
+const char *b200msm_last_error(void);
+
+/* sizeof(GroupT) / sizeof(Fr) for a group id; 0 for an unknown id */
+size_t b200msm_group_bytes(uint32_t group);
+size_t b200msm_scalar_bytes(uint32_t group);
+
+/* libff::multi_exp<G, Fr, multi_exp_method_BDLO12[_signed], form>(bases, scalars, chunks)
+ * (multiexp.tcc:643-688).  bases_bytes == n * sizeof(GroupT), scalars_bytes == n * sizeof(Fr),
+ * out_bytes == sizeof(GroupT).  n == 0 yields the zero element (multiexp.tcc:291-309).
+ * Host pointers; the copies to and from the device happen inside the call. */
+bool b200msm_multi_exp(uint32_t group, const void *bases, size_t bases_bytes, const void *scalars,
+                       size_t scalars_bytes, size_t n, uint32_t base_form, void *out,
+                       size_t out_bytes);
+
+/* The same computation on inputs kept resident in HBM (a prover's fixed bases; scalars of a
+ * batch): upload once, run any sub-range [first, first + n) many times, release. */
+bool b200msm_bases_upload(uint32_t group, const void *bases, size_t bases_bytes, size_t n,
+                          uint32_t base_form, uint64_t *handle);
+bool b200msm_scalars_upload(uint32_t group, const void *scalars, size_t scalars_bytes, size_t n,
+                            uint64_t *handle);
+bool b200msm_multi_exp_resident(uint32_t group, uint64_t bases_handle, uint64_t scalars_handle,
+                                size_t first, size_t n, void *out, size_t out_bytes);
+bool b200msm_release(uint64_t handle);
+
+/* Sum of `count` group elements in reference layout: the reduction of per-chunk partials that
+ * ends libff::multi_exp (multiexp.tcc:681-685); used to combine the partial results of GPU
+ * shards.  points_bytes == count * sizeof(GroupT). */
+bool b200msm_sum(uint32_t group, const void *points, size_t points_bytes, size_t count, void *out,
+                 size_t out_bytes);
+
+/* libff::batch_to_special<G>(vec) (multiexp.tcc:949-974), in place; bytes == n * sizeof(GroupT).
+ * Output is canonical (Z = 1; zero -> (0, 1, 0)) and equals the reference's limb for limb. */
+bool b200msm_batch_to_special(uint32_t group, void *inout, size_t bytes, size_t n);
+
+/* libff::batch_exp<G, Fr>(scalar_size, window, table, v) (multiexp.tcc:875-915).  window_table<G>
+ * is vector<vector<G>> (multiexp.hpp:101): pass one pointer per row, each row `row_len`
+ * (= 1 << window) elements (multiexp.tcc:809-846).  num_rows must equal
+ * ceil(scalar_bits / window).  out_bytes == n * sizeof(GroupT). */
+bool b200msm_batch_exp(uint32_t group, size_t scalar_bits, size_t window,
+                       const void *const *table_rows, size_t num_rows, size_t row_len,
+                       const void *scalars, size_t scalars_bytes, size_t n, void *out,
+                       size_t out_bytes);
+
+/* Tuning and measurement (not part of the reference surface).
+ * option: "window_bits" (0 = automatic), "segment" (entries per thread of the accumulation). */
+bool b200msm_set_option(const char *name, int64_t value);
+/* CUDA-event timings (ms) of the phases of the most recent multi_exp on this thread's engine,
+ * measured on the engine's own stream.  Writes up to `cap` values, returns how many phases exist.
+ * Order: 0 upload/ingest, 1 digits+histogram, 2 scan, 3 scatter, 4 bucket accumulation
+ * (first round), 5 carry rounds, 6 bucket reduction, 7 window reduction + final, 8 total. */
+size_t b200msm_last_timings(float *ms, size_t cap);
+const char *b200msm_timing_name(size_t phase);
+/* number of kernel launches issued by this library since init */
+uint64_t b200msm_launch_count(void);
+/* window bits the engine picks for n points of a group */
+uint32_t b200msm_window_bits(uint32_t group, size_t n);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200MSM_H */

@@ -1,0 +1,313 @@
+"""libff_b200 -- Python-side mirror of the libff MSM surface over the b200msm C ABI.
+
+The product is the C ABI shared library `libff_b200/libb200msm.so` (include/b200msm.h), built from
+the hand-written sm_100a kernels in `libff_b200/csrc`.  This module is a thin ctypes binding whose
+function names, argument meaning and error behaviour follow the reference templates
+
+    libff::multi_exp<G, Fr, Method, BaseForm>(bases, scalars, chunks)   multiexp.tcc:643-688
+    libff::batch_exp<G, Fr>(scalar_size, window, table, v)              multiexp.tcc:875-915
+    libff::batch_to_special<G>(vec)                                     multiexp.tcc:949-974
+
+(paths under libff/algebra/scalar_multiplication/).  Arrays are numpy uint64 in the reference's
+in-memory layout: field elements as little-endian 64-bit Montgomery limbs, group elements as
+X | Y | Z.  There is no CPU fallback: importing works anywhere, but every compute call raises
+`B200MsmError` unless the CUDA library is present and a device is bound.
+
+The C++ drop-in (template specialisations for existing libff call sites) is
+`libff_b200/include/libff_b200.hpp`; see INTEGRATION.md.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional, Sequence
+
+import numpy as np
+
+__all__ = [
+    "ALT_BN128_G1", "ALT_BN128_G2", "BLS12_377_G1", "BW6_761_G1", "GROUP_NAMES",
+    "FORM_NORMAL", "FORM_SPECIAL", "B200MsmError", "lib_path", "load", "init", "shutdown",
+    "group_bytes", "scalar_bytes", "multi_exp", "batch_exp", "batch_to_special", "group_sum",
+    "ResidentBases", "ResidentScalars", "multi_exp_resident", "last_timings", "launch_count",
+    "set_option", "window_bits", "shard_range",
+]
+
+ALT_BN128_G1, ALT_BN128_G2, BLS12_377_G1, BW6_761_G1 = 0, 1, 2, 3
+GROUP_NAMES = {0: "alt_bn128_G1", 1: "alt_bn128_G2", 2: "bls12_377_G1", 3: "bw6_761_G1"}
+FORM_NORMAL, FORM_SPECIAL = 0, 1  # multi_exp_base_form (multiexp.hpp:49-58)
+
+# every symbol include/b200msm.h declares (tests check the library exports all of them)
+ABI_SYMBOLS = [
+    "b200msm_init", "b200msm_shutdown", "b200msm_last_error", "b200msm_group_bytes",
+    "b200msm_scalar_bytes", "b200msm_multi_exp", "b200msm_bases_upload",
+    "b200msm_scalars_upload", "b200msm_multi_exp_resident", "b200msm_release", "b200msm_sum",
+    "b200msm_batch_to_special", "b200msm_batch_exp", "b200msm_set_option",
+    "b200msm_last_timings", "b200msm_timing_name", "b200msm_launch_count", "b200msm_window_bits",
+]
+
+
+class B200MsmError(RuntimeError):
+    pass
+
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_lib = None
+_bound_device: Optional[int] = None
+
+
+def lib_path() -> str:
+    return os.path.join(_HERE, "libb200msm.so")
+
+
+def load():
+    """Loads the C ABI library (no CUDA call is made).  Raises if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = lib_path()
+    if not os.path.exists(path):
+        raise B200MsmError(
+            f"{path} is missing: build it with `make -C libff_b200/csrc -j` (or "
+            "`python -c 'import __graft_entry__ as g; g.build()'`); there is no CPU fallback")
+    L = C.CDLL(path)
+    vp, sz, u32, u64, i64 = C.c_void_p, C.c_size_t, C.c_uint32, C.c_uint64, C.c_int64
+    sigs = {
+        "b200msm_init": (C.c_bool, [C.c_int]),
+        "b200msm_shutdown": (None, []),
+        "b200msm_last_error": (C.c_char_p, []),
+        "b200msm_group_bytes": (sz, [u32]),
+        "b200msm_scalar_bytes": (sz, [u32]),
+        "b200msm_multi_exp": (C.c_bool, [u32, vp, sz, vp, sz, sz, u32, vp, sz]),
+        "b200msm_bases_upload": (C.c_bool, [u32, vp, sz, sz, u32, C.POINTER(u64)]),
+        "b200msm_scalars_upload": (C.c_bool, [u32, vp, sz, sz, C.POINTER(u64)]),
+        "b200msm_multi_exp_resident": (C.c_bool, [u32, u64, u64, sz, sz, vp, sz]),
+        "b200msm_release": (C.c_bool, [u64]),
+        "b200msm_sum": (C.c_bool, [u32, vp, sz, sz, vp, sz]),
+        "b200msm_batch_to_special": (C.c_bool, [u32, vp, sz, sz]),
+        "b200msm_batch_exp": (C.c_bool, [u32, sz, sz, C.POINTER(vp), sz, sz, vp, sz, sz, vp, sz]),
+        "b200msm_set_option": (C.c_bool, [C.c_char_p, i64]),
+        "b200msm_last_timings": (sz, [C.POINTER(C.c_float), sz]),
+        "b200msm_timing_name": (C.c_char_p, [sz]),
+        "b200msm_launch_count": (u64, []),
+        "b200msm_window_bits": (u32, [u32, sz]),
+    }
+    for name, (res, args) in sigs.items():
+        f = getattr(L, name)
+        f.restype = res
+        f.argtypes = args
+    _lib = L
+    return L
+
+
+def _fail(what: str):
+    msg = load().b200msm_last_error()
+    raise B200MsmError(f"{what}: {msg.decode() if msg else 'unknown error'}")
+
+
+def init(device: Optional[int] = None) -> int:
+    """Binds this process to one CUDA device (default: LOCAL_RANK, else 0)."""
+    global _bound_device
+    if device is None:
+        device = int(os.environ.get("LOCAL_RANK", "0"))
+    if not load().b200msm_init(int(device)):
+        _fail("b200msm_init")
+    _bound_device = int(device)
+    return _bound_device
+
+
+def shutdown() -> None:
+    global _bound_device
+    if _lib is not None:
+        _lib.b200msm_shutdown()
+    _bound_device = None
+
+
+def _ensure_init():
+    if _bound_device is None:
+        init()
+
+
+def group_bytes(group: int) -> int:
+    return int(load().b200msm_group_bytes(group))
+
+
+def scalar_bytes(group: int) -> int:
+    return int(load().b200msm_scalar_bytes(group))
+
+
+def _as_u64(a, what: str) -> np.ndarray:
+    a = np.ascontiguousarray(a)
+    if a.dtype != np.uint64:
+        raise B200MsmError(f"{what}: expected uint64 limbs, got {a.dtype}")
+    return a
+
+
+def _ptr(a: np.ndarray):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def _count(a: np.ndarray, elem_bytes: int, what: str) -> int:
+    if a.nbytes % elem_bytes:
+        raise B200MsmError(f"{what}: {a.nbytes} bytes is not a multiple of {elem_bytes}")
+    return a.nbytes // elem_bytes
+
+
+def shard_range(n: int, rank: int, world: int):
+    """Point range of one GPU shard: contiguous ranges, the last takes the remainder -- the
+    reference's own `chunks` split (multiexp.tcc:663-678)."""
+    one = n // world
+    lo = rank * one
+    hi = n if rank == world - 1 else lo + one
+    return lo, hi
+
+
+def multi_exp(group: int, bases, scalars, base_form: int = FORM_SPECIAL,
+              chunks: int = 1) -> np.ndarray:
+    """libff::multi_exp<G, Fr, multi_exp_method_BDLO12, base_form>(bases, scalars, chunks).
+
+    `chunks` is accepted for call-site compatibility and ignored: the reference uses it to split
+    the range over OpenMP threads (multiexp.tcc:655-687); one device consumes the whole range.
+    Returns one group element (3 coordinates) in the reference's layout."""
+    _ensure_init()
+    L = load()
+    b = _as_u64(bases, "bases")
+    s = _as_u64(scalars, "scalars")
+    gb, sb = group_bytes(group), scalar_bytes(group)
+    if gb == 0:
+        raise B200MsmError(f"unknown group id {group}")
+    n = _count(b, gb, "bases")
+    if _count(s, sb, "scalars") != n:
+        raise B200MsmError(f"multi_exp: {n} bases but {_count(s, sb, 'scalars')} scalars")
+    out = np.zeros(gb // 8, dtype=np.uint64)
+    if not L.b200msm_multi_exp(group, _ptr(b), b.nbytes, _ptr(s), s.nbytes, n, base_form,
+                               _ptr(out), out.nbytes):
+        _fail("b200msm_multi_exp")
+    return out
+
+
+def multi_exp_host_ptr(group: int, bases_ptr: int, scalars_ptr: int, n: int,
+                       base_form: int = FORM_SPECIAL) -> np.ndarray:
+    """multi_exp on raw host addresses (e.g. pinned buffers owned by the caller)."""
+    _ensure_init()
+    gb, sb = group_bytes(group), scalar_bytes(group)
+    out = np.zeros(gb // 8, dtype=np.uint64)
+    if not load().b200msm_multi_exp(group, C.c_void_p(bases_ptr), n * gb, C.c_void_p(scalars_ptr),
+                                    n * sb, n, base_form, _ptr(out), out.nbytes):
+        _fail("b200msm_multi_exp")
+    return out
+
+
+def group_sum(group: int, points) -> np.ndarray:
+    """Sum of group elements: the partial-result reduction that ends libff::multi_exp
+    (multiexp.tcc:681-685); combines the per-GPU partial MSMs."""
+    _ensure_init()
+    p = _as_u64(points, "points")
+    gb = group_bytes(group)
+    cnt = _count(p, gb, "points")
+    out = np.zeros(gb // 8, dtype=np.uint64)
+    if not load().b200msm_sum(group, _ptr(p), p.nbytes, cnt, _ptr(out), out.nbytes):
+        _fail("b200msm_sum")
+    return out
+
+
+def batch_to_special(group: int, points) -> np.ndarray:
+    """libff::batch_to_special<G>(vec): returns the normalised copy (the C ABI works in place)."""
+    _ensure_init()
+    p = _as_u64(points, "points").copy()
+    gb = group_bytes(group)
+    n = _count(p, gb, "points")
+    if not load().b200msm_batch_to_special(group, _ptr(p), p.nbytes, n):
+        _fail("b200msm_batch_to_special")
+    return p
+
+
+def batch_exp(group: int, scalar_size: int, window: int, table: Sequence, scalars) -> np.ndarray:
+    """libff::batch_exp<G, Fr>(scalar_size, window, table, v).  `table` is a sequence of rows
+    (window_table<G> = vector<vector<G>>) or a (rows, 1 << window, words) array."""
+    _ensure_init()
+    gb, sb = group_bytes(group), scalar_bytes(group)
+    rows = [_as_u64(r, "table row") for r in table]
+    s = _as_u64(scalars, "scalars")
+    n = _count(s, sb, "scalars")
+    row_len = _count(rows[0], gb, "table row") if rows else 0
+    ptrs = (C.c_void_p * len(rows))(*[r.ctypes.data for r in rows])
+    out = np.zeros((n, gb // 8), dtype=np.uint64)
+    if not load().b200msm_batch_exp(group, scalar_size, window, ptrs, len(rows), row_len, _ptr(s),
+                                    s.nbytes, n, _ptr(out), out.nbytes):
+        _fail("b200msm_batch_exp")
+    return out
+
+
+class _Resident:
+    def __init__(self, handle: int, group: int, n: int):
+        self.handle, self.group, self.n = handle, group, n
+
+    def release(self):
+        if self.handle and _lib is not None:
+            _lib.b200msm_release(self.handle)
+        self.handle = 0
+
+    def __del__(self):
+        try:
+            self.release()
+        except Exception:
+            pass
+
+
+class ResidentBases(_Resident):
+    """Bases kept in HBM (a prover's fixed bases): uploaded and normalised once."""
+
+    def __init__(self, group: int, bases, base_form: int = FORM_SPECIAL):
+        _ensure_init()
+        b = _as_u64(bases, "bases")
+        n = _count(b, group_bytes(group), "bases")
+        h = C.c_uint64(0)
+        if not load().b200msm_bases_upload(group, _ptr(b), b.nbytes, n, base_form, C.byref(h)):
+            _fail("b200msm_bases_upload")
+        super().__init__(h.value, group, n)
+
+
+class ResidentScalars(_Resident):
+    def __init__(self, group: int, scalars):
+        _ensure_init()
+        s = _as_u64(scalars, "scalars")
+        n = _count(s, scalar_bytes(group), "scalars")
+        h = C.c_uint64(0)
+        if not load().b200msm_scalars_upload(group, _ptr(s), s.nbytes, n, C.byref(h)):
+            _fail("b200msm_scalars_upload")
+        super().__init__(h.value, group, n)
+
+
+def multi_exp_resident(bases: ResidentBases, scalars: ResidentScalars, first: int = 0,
+                       n: Optional[int] = None) -> np.ndarray:
+    group = bases.group
+    if n is None:
+        n = bases.n - first
+    out = np.zeros(group_bytes(group) // 8, dtype=np.uint64)
+    if not load().b200msm_multi_exp_resident(group, bases.handle, scalars.handle, first, n,
+                                             _ptr(out), out.nbytes):
+        _fail("b200msm_multi_exp_resident")
+    return out
+
+
+def last_timings() -> dict:
+    """CUDA-event phase timings (ms) of the most recent multi_exp, on the engine's stream."""
+    L = load()
+    buf = (C.c_float * 16)()
+    k = L.b200msm_last_timings(buf, 16)
+    return {L.b200msm_timing_name(i).decode(): float(buf[i]) for i in range(k)}
+
+
+def launch_count() -> int:
+    return int(load().b200msm_launch_count())
+
+
+def set_option(name: str, value: int) -> None:
+    _ensure_init()
+    if not load().b200msm_set_option(name.encode(), int(value)):
+        _fail("b200msm_set_option")
+
+
+def window_bits(group: int, n: int) -> int:
+    _ensure_init()
+    return int(load().b200msm_window_bits(group, n))

@@ -1,0 +1,389 @@
+// extern "C" boundary of the engine (declared in include/b200msm.h).  Conventions follow the
+// reference's ffi layer (ffi/ffi.cpp:16-54,124-260): bool status, exact-size checks, caller-owned
+// buffers, outputs written only on success, no exceptions across the boundary.
+#include "../../include/b200msm.h"
+
+#include <cstring>
+#include <map>
+#include <mutex>
+
+#include "engine.hpp"
+
+namespace b200msm {
+
+static thread_local std::string g_error;
+
+void set_error(const char *fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_error = buf;
+}
+
+bool Ctx::reserve(Slot s, size_t bytes, void **out) {
+    if (bytes == 0) bytes = 16;
+    if (slot_bytes[s] < bytes) {
+        if (slot_ptr[s]) {
+            B200_CUDA(cudaStreamSynchronize(stream));
+            B200_CUDA(cudaFree(slot_ptr[s]));
+            slot_ptr[s] = nullptr;
+            slot_bytes[s] = 0;
+        }
+        size_t want = bytes + bytes / 16;  // a little head-room against near-miss regrowth
+        cudaError_t e = cudaMalloc(&slot_ptr[s], want);
+        if (e != cudaSuccess) {
+            want = bytes;
+            (void)cudaGetLastError();
+            e = cudaMalloc(&slot_ptr[s], want);
+        }
+        if (e != cudaSuccess) {
+            set_error("cudaMalloc of %zu bytes (scratch slot %d) failed: %s", want, (int)s,
+                      cudaGetErrorString(e));
+            slot_ptr[s] = nullptr;
+            return false;
+        }
+        slot_bytes[s] = want;
+    }
+    *out = slot_ptr[s];
+    return true;
+}
+
+void Ctx::release_all() {
+    for (int s = 0; s < SL_COUNT; s++) {
+        if (slot_ptr[s]) cudaFree(slot_ptr[s]);
+        slot_ptr[s] = nullptr;
+        slot_bytes[s] = 0;
+    }
+}
+
+namespace {
+
+struct Resident {
+    uint32_t group;
+    bool is_bases;
+    size_t n;
+    void *data = nullptr;   // affine bases or scalars
+    uint8_t *inf = nullptr; // bases only
+};
+
+std::mutex g_mutex;
+Ctx *g_ctx = nullptr;
+std::map<uint64_t, Resident> g_resident;
+uint64_t g_next_handle = 1;
+
+const GroupOps *ops_for(uint32_t group) {
+    switch (group) {
+        case B200MSM_ALT_BN128_G1: return ops_alt_bn128_g1();
+        case B200MSM_ALT_BN128_G2: return ops_alt_bn128_g2();
+        case B200MSM_BLS12_377_G1: return ops_bls12_377_g1();
+        case B200MSM_BW6_761_G1: return ops_bw6_761_g1();
+    }
+    return nullptr;
+}
+
+bool ready() {
+    if (!g_ctx) {
+        set_error("b200msm_init() has not been called (no CUDA device bound; there is no CPU path)");
+        return false;
+    }
+    B200_CUDA(cudaSetDevice(g_ctx->device));
+    return true;
+}
+
+const GroupOps *checked_ops(uint32_t group) {
+    const GroupOps *ops = ops_for(group);
+    if (!ops) set_error("unknown group id %u", group);
+    return ops;
+}
+
+bool collect_timings(Ctx &ctx) {
+    B200_CUDA(cudaEventRecord(ctx.ev[PH_TOTAL + 1], ctx.stream));
+    B200_CUDA(cudaEventSynchronize(ctx.ev[PH_TOTAL + 1]));
+    for (int p = 0; p < PH_TOTAL; p++)
+        B200_CUDA(cudaEventElapsedTime(&ctx.last_ms[p], ctx.ev[p], ctx.ev[p + 1]));
+    B200_CUDA(cudaEventElapsedTime(&ctx.last_ms[PH_TOTAL], ctx.ev[0], ctx.ev[PH_TOTAL + 1]));
+    ctx.have_timings = true;
+    return true;
+}
+
+// all events of a run must exist on the stream even when a phase is skipped
+bool mark_all(Ctx &ctx, int from) {
+    for (int p = from; p <= PH_TOTAL; p++) B200_CUDA(cudaEventRecord(ctx.ev[p], ctx.stream));
+    return true;
+}
+
+bool run_msm(Ctx &ctx, const GroupOps *ops, const void *d_aff, const uint8_t *d_inf,
+             const void *d_scalars, size_t n, void *out) {
+    void *d_out;
+    if (!ctx.reserve(SL_OUT, ops->group_bytes, &d_out)) return false;
+    if (!mark_all(ctx, PH_INGEST + 1)) return false;
+    if (!ops->msm(ctx, d_aff, d_inf, d_scalars, n, d_out)) return false;
+    std::vector<unsigned char> tmp(ops->group_bytes);
+    B200_CUDA(cudaMemcpyAsync(tmp.data(), d_out, ops->group_bytes, cudaMemcpyDeviceToHost, ctx.stream));
+    if (!collect_timings(ctx)) return false;
+    B200_CUDA(cudaStreamSynchronize(ctx.stream));
+    memcpy(out, tmp.data(), ops->group_bytes);
+    return true;
+}
+
+}  // namespace
+}  // namespace b200msm
+
+using namespace b200msm;
+
+extern "C" {
+
+bool b200msm_init(int device) {
+    std::lock_guard<std::mutex> lk(g_mutex);
+    if (g_ctx) {
+        if (g_ctx->device == device) return true;
+        set_error("already initialised on device %d", g_ctx->device);
+        return false;
+    }
+    int count = 0;
+    B200_CUDA(cudaGetDeviceCount(&count));
+    if (device < 0 || device >= count) {
+        set_error("device %d not available (%d CUDA devices); there is no CPU path", device, count);
+        return false;
+    }
+    B200_CUDA(cudaSetDevice(device));
+    Ctx *ctx = new Ctx();
+    ctx->device = device;
+    B200_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    for (auto &e : ctx->ev) B200_CUDA(cudaEventCreate(&e));
+    g_ctx = ctx;
+    return true;
+}
+
+void b200msm_shutdown(void) {
+    std::lock_guard<std::mutex> lk(g_mutex);
+    if (!g_ctx) return;
+    cudaSetDevice(g_ctx->device);
+    cudaStreamSynchronize(g_ctx->stream);
+    for (auto &kv : g_resident) {
+        cudaFree(kv.second.data);
+        if (kv.second.inf) cudaFree(kv.second.inf);
+    }
+    g_resident.clear();
+    g_ctx->release_all();
+    for (auto &e : g_ctx->ev) cudaEventDestroy(e);
+    cudaStreamDestroy(g_ctx->stream);
+    delete g_ctx;
+    g_ctx = nullptr;
+}
+
+const char *b200msm_last_error(void) { return g_error.c_str(); }
+
+size_t b200msm_group_bytes(uint32_t group) {
+    const GroupOps *o = ops_for(group);
+    return o ? o->group_bytes : 0;
+}
+size_t b200msm_scalar_bytes(uint32_t group) {
+    const GroupOps *o = ops_for(group);
+    return o ? o->scalar_bytes : 0;
+}
+
+bool b200msm_multi_exp(uint32_t group, const void *bases, size_t bases_bytes, const void *scalars,
+                       size_t scalars_bytes, size_t n, uint32_t base_form, void *out,
+                       size_t out_bytes) {
+    std::lock_guard<std::mutex> lk(g_mutex);
+    const GroupOps *ops = checked_ops(group);
+    if (!ops || !ready()) return false;
+    if (base_form > 1) return set_error("invalid base_form %u", base_form), false;
+    if (bases_bytes != n * ops->group_bytes || scalars_bytes != n * ops->scalar_bytes ||
+        out_bytes != ops->group_bytes)
+        return set_error("multi_exp: buffer sizes do not match n = %zu", n), false;
+    if (!out || (n > 0 && (!bases || !scalars))) return set_error("multi_exp: null buffer"), false;
+    Ctx &ctx = *g_ctx;
+    void *d_raw, *d_aff, *d_inf, *d_sc;
+    if (!ctx.reserve(SL_RAW, bases_bytes, &d_raw)) return false;
+    if (!ctx.reserve(SL_AFF, n * ops->affine_bytes, &d_aff)) return false;
+    if (!ctx.reserve(SL_INF, n, &d_inf)) return false;
+    if (!ctx.reserve(SL_SCALARS, scalars_bytes, &d_sc)) return false;
+    B200_CUDA(cudaEventRecord(ctx.ev[0], ctx.stream));
+    if (n > 0) {
+        B200_CUDA(cudaMemcpyAsync(d_raw, bases, bases_bytes, cudaMemcpyHostToDevice, ctx.stream));
+        B200_CUDA(cudaMemcpyAsync(d_sc, scalars, scalars_bytes, cudaMemcpyHostToDevice, ctx.stream));
+        if (!ops->ingest(ctx, d_raw, n, base_form, d_aff, (uint8_t *)d_inf)) return false;
+    }
+    return run_msm(ctx, ops, d_aff, (const uint8_t *)d_inf, d_sc, n, out);
+}
+
+bool b200msm_bases_upload(uint32_t group, const void *bases, size_t bases_bytes, size_t n,
+                          uint32_t base_form, uint64_t *handle) {
+    std::lock_guard<std::mutex> lk(g_mutex);
+    const GroupOps *ops = checked_ops(group);
+    if (!ops || !ready()) return false;
+    if (base_form > 1) return set_error("invalid base_form %u", base_form), false;
+    if (!handle || !bases || n == 0 || bases_bytes != n * ops->group_bytes)
+        return set_error("bases_upload: bad arguments"), false;
+    Ctx &ctx = *g_ctx;
+    Resident r{group, true, n};
+    void *d_raw;
+    if (!ctx.reserve(SL_RAW, bases_bytes, &d_raw)) return false;
+    B200_CUDA(cudaMalloc(&r.data, n * ops->affine_bytes));
+    B200_CUDA(cudaMalloc((void **)&r.inf, n));
+    B200_CUDA(cudaMemcpyAsync(d_raw, bases, bases_bytes, cudaMemcpyHostToDevice, ctx.stream));
+    bool ok = ops->ingest(ctx, d_raw, n, base_form, r.data, r.inf);
+    if (ok && cudaStreamSynchronize(ctx.stream) != cudaSuccess) ok = false, set_error("ingest failed");
+    if (!ok) {
+        cudaFree(r.data);
+        cudaFree(r.inf);
+        return false;
+    }
+    *handle = g_next_handle++;
+    g_resident[*handle] = r;
+    return true;
+}
+
+bool b200msm_scalars_upload(uint32_t group, const void *scalars, size_t scalars_bytes, size_t n,
+                            uint64_t *handle) {
+    std::lock_guard<std::mutex> lk(g_mutex);
+    const GroupOps *ops = checked_ops(group);
+    if (!ops || !ready()) return false;
+    if (!handle || !scalars || n == 0 || scalars_bytes != n * ops->scalar_bytes)
+        return set_error("scalars_upload: bad arguments"), false;
+    Resident r{group, false, n};
+    B200_CUDA(cudaMalloc(&r.data, scalars_bytes));
+    B200_CUDA(cudaMemcpy(r.data, scalars, scalars_bytes, cudaMemcpyHostToDevice));
+    *handle = g_next_handle++;
+    g_resident[*handle] = r;
+    return true;
+}
+
+bool b200msm_multi_exp_resident(uint32_t group, uint64_t bases_handle, uint64_t scalars_handle,
+                                size_t first, size_t n, void *out, size_t out_bytes) {
+    std::lock_guard<std::mutex> lk(g_mutex);
+    const GroupOps *ops = checked_ops(group);
+    if (!ops || !ready()) return false;
+    auto b = g_resident.find(bases_handle), s = g_resident.find(scalars_handle);
+    if (b == g_resident.end() || s == g_resident.end() || !b->second.is_bases || s->second.is_bases ||
+        b->second.group != group || s->second.group != group)
+        return set_error("multi_exp_resident: bad handle"), false;
+    if (first + n > b->second.n || first + n > s->second.n || out_bytes != ops->group_bytes || !out)
+        return set_error("multi_exp_resident: range or size mismatch"), false;
+    Ctx &ctx = *g_ctx;
+    B200_CUDA(cudaEventRecord(ctx.ev[0], ctx.stream));
+    return run_msm(ctx, ops, (const char *)b->second.data + first * ops->affine_bytes,
+                   b->second.inf + first, (const char *)s->second.data + first * ops->scalar_bytes, n,
+                   out);
+}
+
+bool b200msm_release(uint64_t handle) {
+    std::lock_guard<std::mutex> lk(g_mutex);
+    auto it = g_resident.find(handle);
+    if (it == g_resident.end()) return set_error("release: unknown handle"), false;
+    if (g_ctx) cudaSetDevice(g_ctx->device);
+    cudaFree(it->second.data);
+    if (it->second.inf) cudaFree(it->second.inf);
+    g_resident.erase(it);
+    return true;
+}
+
+bool b200msm_sum(uint32_t group, const void *points, size_t points_bytes, size_t count, void *out,
+                 size_t out_bytes) {
+    std::lock_guard<std::mutex> lk(g_mutex);
+    const GroupOps *ops = checked_ops(group);
+    if (!ops || !ready()) return false;
+    if (points_bytes != count * ops->group_bytes || out_bytes != ops->group_bytes || !out ||
+        (count > 0 && !points))
+        return set_error("sum: buffer sizes do not match count = %zu", count), false;
+    Ctx &ctx = *g_ctx;
+    void *d_raw, *d_out;
+    if (!ctx.reserve(SL_RAW, points_bytes, &d_raw)) return false;
+    if (!ctx.reserve(SL_OUT, ops->group_bytes, &d_out)) return false;
+    if (count) B200_CUDA(cudaMemcpyAsync(d_raw, points, points_bytes, cudaMemcpyHostToDevice, ctx.stream));
+    if (!ops->sum(ctx, d_raw, count, d_out)) return false;
+    std::vector<unsigned char> tmp(ops->group_bytes);
+    B200_CUDA(cudaMemcpyAsync(tmp.data(), d_out, ops->group_bytes, cudaMemcpyDeviceToHost, ctx.stream));
+    B200_CUDA(cudaStreamSynchronize(ctx.stream));
+    memcpy(out, tmp.data(), ops->group_bytes);
+    return true;
+}
+
+bool b200msm_batch_to_special(uint32_t group, void *inout, size_t bytes, size_t n) {
+    std::lock_guard<std::mutex> lk(g_mutex);
+    const GroupOps *ops = checked_ops(group);
+    if (!ops || !ready()) return false;
+    if (bytes != n * ops->group_bytes || (n > 0 && !inout))
+        return set_error("batch_to_special: buffer size does not match n = %zu", n), false;
+    if (n == 0) return true;
+    Ctx &ctx = *g_ctx;
+    void *d_raw;
+    if (!ctx.reserve(SL_RAW, bytes, &d_raw)) return false;
+    B200_CUDA(cudaMemcpyAsync(d_raw, inout, bytes, cudaMemcpyHostToDevice, ctx.stream));
+    if (!ops->to_special(ctx, d_raw, n)) return false;
+    // outputs are written only on success: the download is the last step
+    B200_CUDA(cudaStreamSynchronize(ctx.stream));
+    B200_CUDA(cudaMemcpy(inout, d_raw, bytes, cudaMemcpyDeviceToHost));
+    return true;
+}
+
+bool b200msm_batch_exp(uint32_t group, size_t scalar_bits, size_t window,
+                       const void *const *table_rows, size_t num_rows, size_t row_len,
+                       const void *scalars, size_t scalars_bytes, size_t n, void *out,
+                       size_t out_bytes) {
+    std::lock_guard<std::mutex> lk(g_mutex);
+    const GroupOps *ops = checked_ops(group);
+    if (!ops || !ready()) return false;
+    if (window == 0 || window > 24 || row_len != ((size_t)1 << window) ||
+        num_rows != (scalar_bits + window - 1) / window || num_rows == 0 || !table_rows)
+        return set_error("batch_exp: table shape does not match scalar_bits/window"), false;
+    if (scalars_bytes != n * ops->scalar_bytes || out_bytes != n * ops->group_bytes ||
+        (n > 0 && (!scalars || !out)))
+        return set_error("batch_exp: buffer sizes do not match n = %zu", n), false;
+    if (n == 0) return true;
+    Ctx &ctx = *g_ctx;
+    const size_t row_bytes = row_len * ops->group_bytes;
+    void *d_table, *d_sc, *d_out;
+    if (!ctx.reserve(SL_TABLE_RAW, num_rows * row_bytes, &d_table)) return false;
+    if (!ctx.reserve(SL_SCALARS, scalars_bytes, &d_sc)) return false;
+    if (!ctx.reserve(SL_BEXP_OUT, out_bytes, &d_out)) return false;
+    for (size_t r = 0; r < num_rows; r++) {
+        if (!table_rows[r]) return set_error("batch_exp: null table row %zu", r), false;
+        B200_CUDA(cudaMemcpyAsync((char *)d_table + r * row_bytes, table_rows[r], row_bytes,
+                                  cudaMemcpyHostToDevice, ctx.stream));
+    }
+    B200_CUDA(cudaMemcpyAsync(d_sc, scalars, scalars_bytes, cudaMemcpyHostToDevice, ctx.stream));
+    if (!ops->batch_exp(ctx, d_table, num_rows, row_len, (int)window, d_sc, n, d_out)) return false;
+    B200_CUDA(cudaStreamSynchronize(ctx.stream));
+    B200_CUDA(cudaMemcpy(out, d_out, out_bytes, cudaMemcpyDeviceToHost));
+    return true;
+}
+
+bool b200msm_set_option(const char *name, int64_t value) {
+    std::lock_guard<std::mutex> lk(g_mutex);
+    if (!g_ctx) return set_error("set_option before init"), false;
+    if (name && !strcmp(name, "window_bits")) return g_ctx->opt_window_bits = (int)value, true;
+    if (name && !strcmp(name, "segment")) return g_ctx->opt_segment = (int)value, true;
+    return set_error("unknown option %s", name ? name : "(null)"), false;
+}
+
+size_t b200msm_last_timings(float *ms, size_t cap) {
+    std::lock_guard<std::mutex> lk(g_mutex);
+    if (!g_ctx || !g_ctx->have_timings) return 0;
+    for (size_t p = 0; p < (size_t)PH_COUNT && p < cap; p++) ms[p] = g_ctx->last_ms[p];
+    return PH_COUNT;
+}
+
+const char *b200msm_timing_name(size_t phase) {
+    static const char *names[PH_COUNT] = {"ingest", "digits", "scan", "scatter", "accumulate",
+                                          "carry_rounds", "bucket_reduce", "final", "total"};
+    return phase < (size_t)PH_COUNT ? names[phase] : "";
+}
+
+uint64_t b200msm_launch_count(void) {
+    std::lock_guard<std::mutex> lk(g_mutex);
+    return g_ctx ? g_ctx->launches : 0;
+}
+
+uint32_t b200msm_window_bits(uint32_t group, size_t n) {
+    std::lock_guard<std::mutex> lk(g_mutex);
+    const GroupOps *ops = ops_for(group);
+    if (!ops || !g_ctx) return 0;
+    return ops->window_bits(*g_ctx, n);
+}
+
+}  // extern "C"

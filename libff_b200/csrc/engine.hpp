@@ -1,0 +1,114 @@
+// Host-side engine state shared by the per-group translation units (no templates here).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <string>
+#include <vector>
+
+namespace b200msm {
+
+enum Phase {
+    PH_INGEST = 0,
+    PH_DIGITS,
+    PH_SCAN,
+    PH_SCATTER,
+    PH_ACCUM,
+    PH_CARRY,
+    PH_BUCKET_REDUCE,
+    PH_FINAL,
+    PH_TOTAL,
+    PH_COUNT
+};
+
+void set_error(const char *fmt, ...);
+
+#define B200_CUDA(call)                                                                     \
+    do {                                                                                    \
+        cudaError_t e_ = (call);                                                            \
+        if (e_ != cudaSuccess) {                                                            \
+            ::b200msm::set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_),    \
+                                 __FILE__, __LINE__);                                       \
+            return false;                                                                   \
+        }                                                                                   \
+    } while (0)
+
+// Grow-only device scratch slots: the pipeline's buffers are reused across calls so that a
+// steady-state multi_exp performs no cudaMalloc.
+enum Slot {
+    SL_RAW = 0,     // uploaded reference-layout bases
+    SL_AFF,         // device affine bases
+    SL_INF,         // infinity flags
+    SL_SCALARS,     // uploaded scalars
+    SL_DIGITS,
+    SL_HIST,
+    SL_OFFSETS,
+    SL_CURSOR,
+    SL_SORTED,
+    SL_BUCKETS,
+    SL_CARRY_KEY_A,
+    SL_CARRY_PT_A,
+    SL_CARRY_KEY_B,
+    SL_CARRY_PT_B,
+    SL_CHUNKS,
+    SL_WINDOWS,
+    SL_OUT,
+    SL_INV_VAL,
+    SL_INV_PRE,
+    SL_INV_PROD,
+    SL_TABLE_RAW,
+    SL_TABLE_AFF,
+    SL_TABLE_INF,
+    SL_BEXP_OUT,
+    SL_COUNT
+};
+
+struct Ctx {
+    int device = -1;
+    cudaStream_t stream = nullptr;
+    void *slot_ptr[SL_COUNT] = {};
+    size_t slot_bytes[SL_COUNT] = {};
+    cudaEvent_t ev[PH_COUNT + 1] = {};
+    float last_ms[PH_COUNT] = {};
+    bool have_timings = false;
+    uint64_t launches = 0;
+    int opt_window_bits = 0;  // 0 = automatic
+    int opt_segment = 0;      // 0 = default
+
+    bool reserve(Slot s, size_t bytes, void **out);
+    void release_all();
+};
+
+template <class T>
+inline bool reserve_as(Ctx &ctx, Slot s, size_t bytes, T **out) {
+    void *p = nullptr;
+    if (!ctx.reserve(s, bytes, &p)) return false;
+    *out = static_cast<T *>(p);
+    return true;
+}
+
+// Type-erased per-group entry points, implemented once per group in group_*.cu.
+struct GroupOps {
+    uint32_t id;
+    size_t group_bytes, scalar_bytes, affine_bytes;
+    int scalar_bits;
+    // d_raw (reference layout, device) -> d_aff, d_inf
+    bool (*ingest)(Ctx &, const void *d_raw, size_t n, uint32_t form, void *d_aff, uint8_t *d_inf);
+    // the MSM proper; result (reference layout) into d_out
+    bool (*msm)(Ctx &, const void *d_aff, const uint8_t *d_inf, const void *d_scalars, size_t n,
+                void *d_out);
+    bool (*sum)(Ctx &, const void *d_raw, size_t count, void *d_out);
+    bool (*to_special)(Ctx &, void *d_raw, size_t n);
+    bool (*batch_exp)(Ctx &, const void *d_table_raw, size_t rows, size_t row_len, int window,
+                      const void *d_scalars, size_t n, void *d_out);
+    uint32_t (*window_bits)(const Ctx &, size_t n);
+};
+
+const GroupOps *ops_alt_bn128_g1();
+const GroupOps *ops_alt_bn128_g2();
+const GroupOps *ops_bls12_377_g1();
+const GroupOps *ops_bw6_761_g1();
+
+}  // namespace b200msm

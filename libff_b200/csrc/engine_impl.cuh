@@ -1,0 +1,280 @@
+// Templated host orchestration of the device pipelines; instantiated once per group.
+#pragma once
+#include <algorithm>
+
+#include "batch_kernels.cuh"
+#include "engine.hpp"
+#include "msm_kernels.cuh"
+
+namespace b200msm {
+
+#define B200_LAUNCH_CHECK(ctx)            \
+    do {                                  \
+        (ctx).launches++;                 \
+        B200_CUDA(cudaPeekAtLastError()); \
+    } while (0)
+
+inline unsigned cdiv(size_t a, size_t b) { return (unsigned)((a + b - 1) / b); }
+
+// Window size: minimises  n*W*10 + W*2^(c-1)*32  field multiplications (bucket accumulation with
+// 8M+2S mixed additions, bucket reduction with two 12M+2S additions per bucket plus the chunk
+// offset), W = ceil((bits + 1) / c).  The reference's own choice is pippenger_optimal_c
+// (multiexp.tcc:35-40); any c gives the same group element.
+template <class C>
+uint32_t pick_window_bits(const Ctx &ctx, size_t n) {
+    if (ctx.opt_window_bits > 0) return (uint32_t)std::min(std::max(ctx.opt_window_bits, 2), 24);
+    const int bits = C::Fr::Params::BITS;
+    double best = 0;
+    uint32_t best_c = 2;
+    for (uint32_t c = 2; c <= 22; c++) {
+        double W = (double)((bits + 1 + c - 1) / c);
+        double cost = (double)n * W * 10.0 + W * (double)(1u << (c - 1)) * 32.0;
+        if (c == 2 || cost < best) best = cost, best_c = c;
+    }
+    return best_c;
+}
+
+template <class C>
+bool ingest_impl(Ctx &ctx, const void *d_raw, size_t n, uint32_t form, void *d_aff, uint8_t *d_inf);
+template <class C>
+bool to_special_impl(Ctx &ctx, void *d_raw, size_t n);
+
+// ------------------------------------------------------------------------------------------
+// 1 / val[i] for n field elements (in place)
+template <class F>
+bool batch_invert_dev(Ctx &ctx, uint32_t *val, size_t n) {
+    // level sizes n0 = n, n1 = ceil(n0 / CHUNK), ... until <= CHUNK
+    std::vector<size_t> sizes{n};
+    while (sizes.back() > (size_t)INV_CHUNK) sizes.push_back((sizes.back() + INV_CHUNK - 1) / INV_CHUNK);
+    size_t pre_total = 0, prod_total = 0;
+    for (size_t l = 0; l < sizes.size(); l++) {
+        pre_total += sizes[l];
+        if (l > 0) prod_total += sizes[l];
+    }
+    uint32_t *pre, *prod;
+    const size_t eb = sizeof(uint32_t) * F::N;
+    if (!reserve_as(ctx, SL_INV_PRE, pre_total * eb, &pre)) return false;
+    if (!reserve_as(ctx, SL_INV_PROD, std::max<size_t>(prod_total, 1) * eb, &prod)) return false;
+    std::vector<uint32_t *> lv_val{val}, lv_pre{pre};
+    {
+        uint32_t *pp = pre + sizes[0] * F::N, *pr = prod;
+        for (size_t l = 1; l < sizes.size(); l++) {
+            lv_val.push_back(pr);
+            lv_pre.push_back(pp);
+            pr += sizes[l] * F::N;
+            pp += sizes[l] * F::N;
+        }
+    }
+    const size_t L = sizes.size();
+    for (size_t l = 0; l + 1 < L; l++) {
+        unsigned threads = (unsigned)sizes[l + 1];
+        k_inv_up<F><<<cdiv(threads, 128), 128, 0, ctx.stream>>>(lv_val[l], lv_pre[l], lv_val[l + 1],
+                                                              (uint32_t)sizes[l]);
+        B200_LAUNCH_CHECK(ctx);
+    }
+    k_inv_root<F><<<1, 32, 0, ctx.stream>>>(lv_val[L - 1], lv_pre[L - 1], (uint32_t)sizes[L - 1]);
+    B200_LAUNCH_CHECK(ctx);
+    for (size_t l = L - 1; l-- > 0;) {
+        unsigned threads = (unsigned)sizes[l + 1];
+        k_inv_down<F><<<cdiv(threads, 128), 128, 0, ctx.stream>>>(lv_val[l], lv_pre[l], lv_val[l + 1],
+                                                                (uint32_t)sizes[l]);
+        B200_LAUNCH_CHECK(ctx);
+    }
+    return true;
+}
+
+// Normalises n reference-layout points; writes reference layout (out_raw, may alias raw) and/or
+// device affine + flags.
+template <class C>
+bool normalise_dev(Ctx &ctx, const uint32_t *raw, size_t n, uint32_t *out_raw, uint32_t *aff,
+                   uint8_t *inf) {
+    using F = typename C::Fq;
+    if (n == 0) return true;
+    uint32_t *z;
+    if (!reserve_as(ctx, SL_INV_VAL, n * sizeof(uint32_t) * F::N, &z)) return false;
+    k_extract_z<C><<<cdiv(n, 128), 128, 0, ctx.stream>>>(raw, z, (uint32_t)n);
+    B200_LAUNCH_CHECK(ctx);
+    if (!batch_invert_dev<F>(ctx, z, n)) return false;
+    k_apply_zinv<C><<<cdiv(n, 128), 128, 0, ctx.stream>>>(raw, z, out_raw, aff, inf, (uint32_t)n);
+    B200_LAUNCH_CHECK(ctx);
+    return true;
+}
+
+template <class C>
+bool to_special_impl(Ctx &ctx, void *d_raw, size_t n) {
+    return normalise_dev<C>(ctx, (const uint32_t *)d_raw, n, (uint32_t *)d_raw, nullptr, nullptr);
+}
+
+template <class C>
+bool ingest_impl(Ctx &ctx, const void *d_raw, size_t n, uint32_t form, void *d_aff, uint8_t *d_inf) {
+    if (n == 0) return true;
+    if (form == 1) {
+        k_ingest_special<C><<<cdiv(n, 128), 128, 0, ctx.stream>>>((const uint32_t *)d_raw,
+                                                                (uint32_t *)d_aff, d_inf, (uint32_t)n);
+        B200_LAUNCH_CHECK(ctx);
+        return true;
+    }
+    return normalise_dev<C>(ctx, (const uint32_t *)d_raw, n, nullptr, (uint32_t *)d_aff, d_inf);
+}
+
+template <class C>
+bool sum_impl(Ctx &ctx, const void *d_raw, size_t count, void *d_out) {
+    k_sum_raw<C><<<1, 32, 0, ctx.stream>>>((const uint32_t *)d_raw, (uint32_t)count, (uint32_t *)d_out);
+    B200_LAUNCH_CHECK(ctx);
+    return true;
+}
+
+// ------------------------------------------------------------------------------------------
+constexpr int SEG_FIRST = 32;   // sorted entries per thread, first accumulation round
+constexpr int SEG_CARRY = 16;   // carries per thread, later rounds
+
+template <class C>
+bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_scalars, size_t n,
+              void *d_out) {
+    using R = Raw<C>;
+    using F = typename C::Fq;
+    cudaStream_t st = ctx.stream;
+    if (n == 0) {  // multiexp.tcc:291-309: zero element
+        k_sum_raw<C><<<1, 32, 0, st>>>(nullptr, 0, (uint32_t *)d_out);
+        B200_LAUNCH_CHECK(ctx);
+        return true;
+    }
+    if (n >= (1ull << 31)) {
+        set_error("multi_exp: n = %zu exceeds the 2^31 - 1 points one device shard addresses", n);
+        return false;
+    }
+    const int c = (int)pick_window_bits<C>(ctx, n);
+    const int W = (C::Fr::Params::BITS + 1 + c - 1) / c;
+    const uint32_t B = 1u << (c - 1);
+    const size_t M = (size_t)W * B;
+    if ((uint64_t)n * W >= (1ull << 32)) {
+        set_error("multi_exp: n * windows = %llu does not fit 32-bit positions",
+                  (unsigned long long)n * W);
+        return false;
+    }
+    int32_t *digits;
+    uint32_t *hist, *offsets, *cursor, *buckets, *chunks, *windows;
+    Entry *sorted;
+    if (!reserve_as(ctx, SL_DIGITS, (size_t)W * n * 4, &digits)) return false;
+    if (!reserve_as(ctx, SL_HIST, M * 4, &hist)) return false;
+    if (!reserve_as(ctx, SL_OFFSETS, (M + 1) * 4, &offsets)) return false;
+    if (!reserve_as(ctx, SL_CURSOR, M * 4, &cursor)) return false;
+    if (!reserve_as(ctx, SL_SORTED, (size_t)W * n * sizeof(Entry), &sorted)) return false;
+    if (!reserve_as(ctx, SL_BUCKETS, M * R::XW * 4, &buckets)) return false;
+
+    // --- digits + histogram
+    B200_CUDA(cudaMemsetAsync(hist, 0, M * 4, st));
+    k_digits<C><<<cdiv(n, 256), 256, 0, st>>>((const uint32_t *)d_scalars, d_inf, digits, hist,
+                                               (uint32_t)n, c, W);
+    B200_LAUNCH_CHECK(ctx);
+    B200_CUDA(cudaEventRecord(ctx.ev[PH_DIGITS + 1], st));
+    // --- offsets
+    k_scan<<<1, 1024, 0, st>>>(hist, offsets, cursor, (uint32_t)M);
+    B200_LAUNCH_CHECK(ctx);
+    B200_CUDA(cudaEventRecord(ctx.ev[PH_SCAN + 1], st));
+    // --- scatter
+    k_scatter<C><<<dim3(cdiv(n, 256), W), 256, 0, st>>>(digits, cursor, sorted, (uint32_t)n, c);
+    B200_LAUNCH_CHECK(ctx);
+    B200_CUDA(cudaEventRecord(ctx.ev[PH_SCATTER + 1], st));
+    // the number of sorted entries is known only on the device; it is needed for launch sizing
+    uint32_t total = 0;
+    B200_CUDA(cudaMemcpyAsync(&total, offsets + M, 4, cudaMemcpyDeviceToHost, st));
+    B200_CUDA(cudaStreamSynchronize(st));
+
+    // --- accumulation rounds
+    if (total > 0) {
+        size_t t1 = ((size_t)total + SEG_FIRST - 1) / SEG_FIRST;
+        size_t t2 = (t1 + SEG_CARRY - 1) / SEG_CARRY;
+        uint32_t *keyA, *ptA, *keyB, *ptB;
+        if (!reserve_as(ctx, SL_CARRY_KEY_A, t1 * 4, &keyA)) return false;
+        if (!reserve_as(ctx, SL_CARRY_PT_A, t1 * R::XW * 4, &ptA)) return false;
+        if (!reserve_as(ctx, SL_CARRY_KEY_B, t2 * 4, &keyB)) return false;
+        if (!reserve_as(ctx, SL_CARRY_PT_B, t2 * R::XW * 4, &ptB)) return false;
+        k_accum_first<C, SEG_FIRST><<<cdiv(t1, 128), 128, 0, st>>>(
+            sorted, total, (const uint32_t *)d_aff, buckets, keyA, ptA);
+        B200_LAUNCH_CHECK(ctx);
+        B200_CUDA(cudaEventRecord(ctx.ev[PH_ACCUM + 1], st));
+        size_t len = t1;
+        while (true) {
+            size_t tn = (len + SEG_CARRY - 1) / SEG_CARRY;
+            k_accum_carry<C, SEG_CARRY><<<cdiv(tn, 128), 128, 0, st>>>(keyA, ptA, (uint32_t)len,
+                                                                       buckets, keyB, ptB);
+            B200_LAUNCH_CHECK(ctx);
+            if (tn == 1) break;  // a single thread owns every run it sees: no carries remain
+            std::swap(keyA, keyB);
+            std::swap(ptA, ptB);
+            len = tn;
+        }
+    } else {
+        B200_CUDA(cudaEventRecord(ctx.ev[PH_ACCUM + 1], st));
+    }
+    B200_CUDA(cudaEventRecord(ctx.ev[PH_CARRY + 1], st));
+
+    // --- bucket reduction
+    uint32_t K = 16;
+    while ((M / K) > 131072 && K < 128) K <<= 1;
+    K = std::min(K, B);
+    const uint32_t nchunks = (B + K - 1) / K;
+    if (!reserve_as(ctx, SL_CHUNKS, (size_t)W * nchunks * R::XW * 4, &chunks)) return false;
+    if (!reserve_as(ctx, SL_WINDOWS, (size_t)W * R::XW * 4, &windows)) return false;
+    k_bucket_reduce<C><<<dim3(cdiv(nchunks, 64), W), 64, 0, st>>>(buckets, hist, B, K, chunks);
+    B200_LAUNCH_CHECK(ctx);
+    B200_CUDA(cudaEventRecord(ctx.ev[PH_BUCKET_REDUCE + 1], st));
+    constexpr int WR_THREADS = 64;
+    const size_t wr_smem = (size_t)WR_THREADS * R::XW * 4;
+    static bool attr_set = false;
+    if (!attr_set) {
+        B200_CUDA(cudaFuncSetAttribute(k_window_reduce<C, WR_THREADS>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wr_smem));
+        attr_set = true;
+    }
+    k_window_reduce<C, WR_THREADS><<<W, WR_THREADS, wr_smem, st>>>(chunks, nchunks, windows);
+    B200_LAUNCH_CHECK(ctx);
+    k_final<C><<<1, 32, 0, st>>>(windows, W, c, (uint32_t *)d_out);
+    B200_LAUNCH_CHECK(ctx);
+    B200_CUDA(cudaEventRecord(ctx.ev[PH_FINAL + 1], st));
+    return true;
+}
+
+template <class C>
+bool batch_exp_impl(Ctx &ctx, const void *d_table_raw, size_t rows, size_t row_len, int window,
+                    const void *d_scalars, size_t n, void *d_out) {
+    using R = Raw<C>;
+    const size_t entries = rows * row_len;
+    uint32_t *taff;
+    uint8_t *tinf;
+    if (!reserve_as(ctx, SL_TABLE_AFF, entries * R::AW * 4, &taff)) return false;
+    if (!reserve_as(ctx, SL_TABLE_INF, entries, &tinf)) return false;
+    // table entries are arbitrary Jacobian/projective representatives: normalise once
+    if (!normalise_dev<C>(ctx, (const uint32_t *)d_table_raw, entries, nullptr, taff, tinf)) return false;
+    if (n == 0) return true;
+    k_batch_exp<C><<<cdiv(n, 128), 128, 0, ctx.stream>>>((const uint32_t *)d_scalars, taff,
+                                                         (uint32_t)rows, (uint32_t)row_len, window,
+                                                         (uint32_t *)d_out, (uint32_t)n);
+    B200_LAUNCH_CHECK(ctx);
+    return true;
+}
+
+template <class C>
+uint32_t window_bits_impl(const Ctx &ctx, size_t n) {
+    return pick_window_bits<C>(ctx, n);
+}
+
+template <class C>
+const GroupOps *make_ops() {
+    using R = Raw<C>;
+    static const GroupOps ops = {(uint32_t)C::ID,
+                                 (size_t)R::PW * 4,
+                                 (size_t)R::SW * 4,
+                                 (size_t)R::AW * 4,
+                                 C::Fr::Params::BITS,
+                                 &ingest_impl<C>,
+                                 &msm_impl<C>,
+                                 &sum_impl<C>,
+                                 &to_special_impl<C>,
+                                 &batch_exp_impl<C>,
+                                 &window_bits_impl<C>};
+    return &ops;
+}
+
+}  // namespace b200msm

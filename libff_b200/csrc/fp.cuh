@@ -1,0 +1,285 @@
+// Prime-field arithmetic on 32-bit limbs held in registers (sm_100a).
+//
+// Replaces the reference's Fp_model<n, modulus> hot leaves:
+//   mul_reduce      libff/algebra/fields/fp.tcc:50-228   (x86 CIOS asm / GMP)  -> Fp::mul / Fp::sqr
+//   operator+= / -= libff/algebra/fields/fp.tcc:350-547                          -> Fp::add / Fp::sub
+//   operator-()     libff/algebra/fields/fp.tcc:616-630                          -> Fp::neg
+//   invert          libff/algebra/fields/fp.tcc:679-727  (mpn_gcdext)            -> Fp::inv (Fermat)
+//   as_bigint       libff/algebra/fields/fp.tcc:270-281                          -> Fp::from_mont
+//
+// Representation contract: an element is the reference's `mont_repr`, x*R mod p with
+// R = 2^(64 n) = 2^(32 N); reinterpreting the host's little-endian 64-bit limbs as 2n 32-bit limbs
+// is a no-op, so uploads/downloads need no conversion.  Every routine returns a canonical
+// representative in [0, p), exactly like the reference, so outputs compare limb for limb.
+//
+// Multiplication is a word-serial Montgomery product on two interleaved accumulators ("even"
+// columns and "odd" columns).  The a[j]*b_i partial products of even j land on register pairs
+// (j, j+1) of one accumulator and those of odd j on pairs of the other, so every
+// mad.lo.cc/madc.hi.cc couple is a single carry chain step on an aligned 64-bit register pair;
+// ptxas turns each couple into one IMAD.WIDE.U32.X.  The one-limb right shift of the reduction
+// step is free: the two accumulators swap roles each row.  All moduli on this path leave at least
+// two spare bits in the top limb, which is what keeps the accumulators from overflowing.
+#pragma once
+#include <cstdint>
+#include "field_params.cuh"
+
+namespace b200msm {
+
+#define B200_DEV __device__ __forceinline__
+
+namespace limb {
+
+// acc[j], acc[j+1] = a[j] * bi for even j < N
+template <int N>
+B200_DEV void row_set(uint32_t *acc, const uint32_t *a, uint32_t bi) {
+#pragma unroll
+    for (int j = 0; j < N; j += 2) {
+        asm("mul.lo.u32 %0, %1, %2;" : "=r"(acc[j]) : "r"(a[j]), "r"(bi));
+        asm("mul.hi.u32 %0, %1, %2;" : "=r"(acc[j + 1]) : "r"(a[j]), "r"(bi));
+    }
+}
+
+// acc[j], acc[j+1] += a[j] * bi for even j < N, one carry chain; carry-out stays in CC
+template <int N>
+B200_DEV void row_acc(uint32_t *acc, const uint32_t *a, uint32_t bi) {
+    asm("mad.lo.cc.u32 %0, %1, %2, %0;" : "+r"(acc[0]) : "r"(a[0]), "r"(bi));
+    asm("madc.hi.cc.u32 %0, %1, %2, %0;" : "+r"(acc[1]) : "r"(a[0]), "r"(bi));
+#pragma unroll
+    for (int j = 2; j < N; j += 2) {
+        asm("madc.lo.cc.u32 %0, %1, %2, %0;" : "+r"(acc[j]) : "r"(a[j]), "r"(bi));
+        asm("madc.hi.cc.u32 %0, %1, %2, %0;" : "+r"(acc[j + 1]) : "r"(a[j]), "r"(bi));
+    }
+}
+
+// acc[j], acc[j+1] = a[j] * bi + acc[j+2], acc[j+3] (+ carry-in from CC): accumulate while
+// dropping the two consumed low limbs
+template <int N>
+B200_DEV void row_acc_shift(uint32_t *acc, const uint32_t *a, uint32_t bi) {
+#pragma unroll
+    for (int j = 0; j < N - 2; j += 2) {
+        asm("madc.lo.cc.u32 %0, %1, %2, %3;" : "=r"(acc[j]) : "r"(a[j]), "r"(bi), "r"(acc[j + 2]));
+        asm("madc.hi.cc.u32 %0, %1, %2, %3;"
+            : "=r"(acc[j + 1])
+            : "r"(a[j]), "r"(bi), "r"(acc[j + 3]));
+    }
+    asm("madc.lo.cc.u32 %0, %1, %2, 0;" : "=r"(acc[N - 2]) : "r"(a[N - 2]), "r"(bi));
+    asm("madc.hi.u32 %0, %1, %2, 0;" : "=r"(acc[N - 1]) : "r"(a[N - 2]), "r"(bi));
+}
+
+}  // namespace limb
+
+template <class P>
+struct Fp {
+    static constexpr int N = P::N;
+    using Params = P;
+    uint32_t v[N];
+
+    B200_DEV static Fp zero() {
+        Fp r;
+#pragma unroll
+        for (int i = 0; i < N; i++) r.v[i] = 0;
+        return r;
+    }
+    B200_DEV static Fp one() {
+        Fp r;
+#pragma unroll
+        for (int i = 0; i < N; i++) r.v[i] = P::one(i);
+        return r;
+    }
+    B200_DEV bool is_zero() const {
+        uint32_t o = v[0];
+#pragma unroll
+        for (int i = 1; i < N; i++) o |= v[i];
+        return o == 0;
+    }
+    B200_DEV bool operator==(const Fp &b) const {
+        uint32_t o = v[0] ^ b.v[0];
+#pragma unroll
+        for (int i = 1; i < N; i++) o |= v[i] ^ b.v[i];
+        return o == 0;
+    }
+
+    // r = a - p if a >= p else a     (a < 2p)
+    B200_DEV static Fp reduce_once(const Fp &a) {
+        Fp s;
+        asm("sub.cc.u32 %0, %1, %2;" : "=r"(s.v[0]) : "r"(a.v[0]), "r"(P::mod(0)));
+#pragma unroll
+        for (int i = 1; i < N; i++)
+            asm("subc.cc.u32 %0, %1, %2;" : "=r"(s.v[i]) : "r"(a.v[i]), "r"(P::mod(i)));
+        uint32_t borrow;
+        asm("subc.u32 %0, 0, 0;" : "=r"(borrow));
+        Fp r;
+#pragma unroll
+        for (int i = 0; i < N; i++) r.v[i] = borrow ? a.v[i] : s.v[i];
+        return r;
+    }
+
+    // fp.tcc:350-465 -- top limb has spare bits, so a + b never carries out of N limbs
+    B200_DEV static Fp add(const Fp &a, const Fp &b) {
+        Fp t;
+        asm("add.cc.u32 %0, %1, %2;" : "=r"(t.v[0]) : "r"(a.v[0]), "r"(b.v[0]));
+#pragma unroll
+        for (int i = 1; i < N - 1; i++)
+            asm("addc.cc.u32 %0, %1, %2;" : "=r"(t.v[i]) : "r"(a.v[i]), "r"(b.v[i]));
+        asm("addc.u32 %0, %1, %2;" : "=r"(t.v[N - 1]) : "r"(a.v[N - 1]), "r"(b.v[N - 1]));
+        return reduce_once(t);
+    }
+    B200_DEV static Fp dbl(const Fp &a) { return add(a, a); }
+
+    // fp.tcc:467-547
+    B200_DEV static Fp sub(const Fp &a, const Fp &b) {
+        Fp t;
+        asm("sub.cc.u32 %0, %1, %2;" : "=r"(t.v[0]) : "r"(a.v[0]), "r"(b.v[0]));
+#pragma unroll
+        for (int i = 1; i < N; i++)
+            asm("subc.cc.u32 %0, %1, %2;" : "=r"(t.v[i]) : "r"(a.v[i]), "r"(b.v[i]));
+        uint32_t borrow;
+        asm("subc.u32 %0, 0, 0;" : "=r"(borrow));  // 0 or 0xffffffff
+        Fp r;
+        asm("add.cc.u32 %0, %1, %2;" : "=r"(r.v[0]) : "r"(t.v[0]), "r"(P::mod(0) & borrow));
+#pragma unroll
+        for (int i = 1; i < N - 1; i++)
+            asm("addc.cc.u32 %0, %1, %2;" : "=r"(r.v[i]) : "r"(t.v[i]), "r"(P::mod(i) & borrow));
+        asm("addc.u32 %0, %1, %2;"
+            : "=r"(r.v[N - 1])
+            : "r"(t.v[N - 1]), "r"(P::mod(N - 1) & borrow));
+        return r;
+    }
+
+    // fp.tcc:616-630 -- the negative of zero is zero
+    B200_DEV static Fp neg(const Fp &a) {
+        uint32_t nz = a.is_zero() ? 0u : 0xffffffffu;
+        Fp r;
+        asm("sub.cc.u32 %0, %1, %2;" : "=r"(r.v[0]) : "r"(P::mod(0) & nz), "r"(a.v[0]));
+#pragma unroll
+        for (int i = 1; i < N - 1; i++)
+            asm("subc.cc.u32 %0, %1, %2;" : "=r"(r.v[i]) : "r"(P::mod(i) & nz), "r"(a.v[i]));
+        asm("subc.u32 %0, %1, %2;" : "=r"(r.v[N - 1]) : "r"(P::mod(N - 1) & nz), "r"(a.v[N - 1]));
+        return r;
+    }
+    B200_DEV static Fp cneg(const Fp &a, bool flag) {
+        Fp n = neg(a);
+        Fp r;
+#pragma unroll
+        for (int i = 0; i < N; i++) r.v[i] = flag ? n.v[i] : a.v[i];
+        return r;
+    }
+    B200_DEV static Fp select(bool flag, const Fp &a, const Fp &b) {  // flag ? a : b
+        Fp r;
+#pragma unroll
+        for (int i = 0; i < N; i++) r.v[i] = flag ? a.v[i] : b.v[i];
+        return r;
+    }
+
+    // One row of the Montgomery product: T += a*bi; m = T[0]*INV; T += m*p; T >>= 32, with
+    // T = E + (O << 32).  On return the roles of E and O are swapped for the caller.
+    B200_DEV static void mont_row(uint32_t *E, uint32_t *O, const uint32_t *a, uint32_t bi,
+                                  bool first) {
+        uint32_t mod[N];
+#pragma unroll
+        for (int i = 0; i < N; i++) mod[i] = P::mod(i);
+        if (first) {
+            limb::row_set<N>(O, a + 1, bi);
+            limb::row_set<N>(E, a, bi);
+        } else {
+            asm("add.cc.u32 %0, %0, %1;" : "+r"(E[0]) : "r"(O[1]));
+            limb::row_acc_shift<N>(O, a + 1, bi);
+            limb::row_acc<N>(E, a, bi);
+            asm("addc.u32 %0, %0, 0;" : "+r"(O[N - 1]));
+        }
+        uint32_t m = E[0] * P::INV;
+        limb::row_acc<N>(O, mod + 1, m);
+        // O never carries out of N limbs (T < 2^(32(N+1))); this keeps the flag dead
+        asm("addc.u32 %0, %0, 0;" : "+r"(O[N - 1]));
+        limb::row_acc<N>(E, mod, m);
+        asm("addc.u32 %0, %0, 0;" : "+r"(O[N - 1]));
+    }
+
+    // fp.tcc:50-228: a*b*R^-1 mod p, canonical.  Wide fields call one shared copy of the
+    // product (a 24-limb product is ~1300 instructions; inlining a dozen per group operation
+    // only thrashes the instruction cache and the compiler).
+    B200_DEV static Fp mul(const Fp &a, const Fp &b) {
+        if constexpr (N >= 24)
+            return mul_call(a, b);
+        else
+            return mul_inline(a, b);
+    }
+    __device__ __noinline__ static Fp mul_call(const Fp &a, const Fp &b) { return mul_inline(a, b); }
+    B200_DEV static Fp mul_inline(const Fp &a, const Fp &b) {
+        uint32_t E[N], O[N];
+#pragma unroll
+        for (int i = 0; i < N; i += 2) {
+            mont_row(E, O, a.v, b.v[i], i == 0);
+            mont_row(O, E, a.v, b.v[i + 1], false);
+        }
+        Fp t;
+        asm("add.cc.u32 %0, %1, %2;" : "=r"(t.v[0]) : "r"(E[0]), "r"(O[1]));
+#pragma unroll
+        for (int i = 1; i < N - 1; i++)
+            asm("addc.cc.u32 %0, %1, %2;" : "=r"(t.v[i]) : "r"(E[i]), "r"(O[i + 1]));
+        asm("addc.u32 %0, %1, 0;" : "=r"(t.v[N - 1]) : "r"(E[N - 1]));
+        return reduce_once(t);
+    }
+    B200_DEV static Fp sqr(const Fp &a) { return mul(a, a); }
+
+    // Montgomery -> plain integer (fp.tcc:270-281): one reduction of (a, 0, ..., 0)
+    B200_DEV static Fp from_mont(const Fp &a) {
+        Fp o = zero();
+        o.v[0] = 1;
+        return mul(a, o);
+    }
+    // plain integer (< p) -> Montgomery (fp.tcc:230-235)
+    B200_DEV static Fp to_mont(const Fp &a) {
+        Fp r2;
+#pragma unroll
+        for (int i = 0; i < N; i++) r2.v[i] = P::r2(i);
+        return mul(a, r2);
+    }
+
+    // a^(p-2): the canonical inverse, equal to the reference's invert() output (the inverse in
+    // [0, p) is unique).  inv(0) = 0.
+    __device__ __noinline__ static Fp inv(const Fp &a) {
+        Fp r = one();
+#pragma unroll 1
+        for (int i = P::BITS - 1; i >= 0; i--) {
+            r = sqr(r);
+            uint32_t w = 0;
+            // p-2 limb lookup without a dynamically indexed local array
+#pragma unroll
+            for (int k = 0; k < N; k++)
+                if ((i >> 5) == k) w = P::pm2(k);
+            if ((w >> (i & 31)) & 1) r = mul(r, a);
+        }
+        return r;
+    }
+
+    B200_DEV static Fp load(const uint32_t *p) {
+        Fp r;
+        if constexpr (N % 4 == 0) {
+#pragma unroll
+            for (int i = 0; i < N; i += 4) {
+                uint4 q = *reinterpret_cast<const uint4 *>(p + i);
+                r.v[i] = q.x, r.v[i + 1] = q.y, r.v[i + 2] = q.z, r.v[i + 3] = q.w;
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < N; i += 2) {
+                uint2 q = *reinterpret_cast<const uint2 *>(p + i);
+                r.v[i] = q.x, r.v[i + 1] = q.y;
+            }
+        }
+        return r;
+    }
+    B200_DEV void store(uint32_t *p) const {
+        if constexpr (N % 4 == 0) {
+#pragma unroll
+            for (int i = 0; i < N; i += 4)
+                *reinterpret_cast<uint4 *>(p + i) = make_uint4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+        } else {
+#pragma unroll
+            for (int i = 0; i < N; i += 2) *reinterpret_cast<uint2 *>(p + i) = make_uint2(v[i], v[i + 1]);
+        }
+    }
+};
+
+}  // namespace b200msm

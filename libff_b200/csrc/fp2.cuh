@@ -1,0 +1,61 @@
+// Quadratic extension Fq2 = Fq[u]/(u^2 + 1) for alt_bn128 G2 coordinates.
+//
+// Replaces Fp2_model (libff/algebra/fields/fp2.tcc): mul :101-114 (Karatsuba), squared_complex
+// :141-151, inverse :153-168, add/sub/neg :79-120.  The reference multiplies by `non_residue`
+// with a full Fq multiplication; for alt_bn128 non_residue = q - 1 = -1
+// (alt_bn128_init.cpp:138-140), so here it is a subtraction -- same value, canonical result.
+// Memory layout = the reference's: c0 limbs then c1 limbs (fp2.hpp `Fp_model coeffs[2]`).
+#pragma once
+#include "fp.cuh"
+
+namespace b200msm {
+
+template <class P>
+struct Fp2 {
+    using F = Fp<P>;
+    static constexpr int N = 2 * P::N;  // 32-bit words per element
+    using Params = P;
+    F c0, c1;
+
+    B200_DEV static Fp2 zero() { return Fp2{F::zero(), F::zero()}; }
+    B200_DEV static Fp2 one() { return Fp2{F::one(), F::zero()}; }
+    B200_DEV bool is_zero() const { return c0.is_zero() && c1.is_zero(); }
+    B200_DEV bool operator==(const Fp2 &b) const { return c0 == b.c0 && c1 == b.c1; }
+    B200_DEV static Fp2 add(const Fp2 &a, const Fp2 &b) {
+        return Fp2{F::add(a.c0, b.c0), F::add(a.c1, b.c1)};
+    }
+    B200_DEV static Fp2 dbl(const Fp2 &a) { return add(a, a); }
+    B200_DEV static Fp2 sub(const Fp2 &a, const Fp2 &b) {
+        return Fp2{F::sub(a.c0, b.c0), F::sub(a.c1, b.c1)};
+    }
+    B200_DEV static Fp2 neg(const Fp2 &a) { return Fp2{F::neg(a.c0), F::neg(a.c1)}; }
+    B200_DEV static Fp2 cneg(const Fp2 &a, bool f) { return Fp2{F::cneg(a.c0, f), F::cneg(a.c1, f)}; }
+    B200_DEV static Fp2 select(bool f, const Fp2 &a, const Fp2 &b) {
+        return Fp2{F::select(f, a.c0, b.c0), F::select(f, a.c1, b.c1)};
+    }
+    // (a0 + a1 u)(b0 + b1 u) = (a0 b0 - a1 b1) + ((a0 + a1)(b0 + b1) - a0 b0 - a1 b1) u
+    __device__ __noinline__ static Fp2 mul(const Fp2 &a, const Fp2 &b) {
+        F v0 = F::mul(a.c0, b.c0);
+        F v1 = F::mul(a.c1, b.c1);
+        F s = F::mul(F::add(a.c0, a.c1), F::add(b.c0, b.c1));
+        return Fp2{F::sub(v0, v1), F::sub(F::sub(s, v0), v1)};
+    }
+    // (a0 + a1 u)^2 = (a0 + a1)(a0 - a1) + 2 a0 a1 u
+    __device__ __noinline__ static Fp2 sqr(const Fp2 &a) {
+        F t = F::mul(a.c0, a.c1);
+        F c0 = F::mul(F::add(a.c0, a.c1), F::sub(a.c0, a.c1));
+        return Fp2{c0, F::dbl(t)};
+    }
+    // 1 / (a0 + a1 u) = (a0 - a1 u) / (a0^2 + a1^2)
+    __device__ __noinline__ static Fp2 inv(const Fp2 &a) {
+        F d = F::inv(F::add(F::sqr(a.c0), F::sqr(a.c1)));
+        return Fp2{F::mul(a.c0, d), F::neg(F::mul(a.c1, d))};
+    }
+    B200_DEV static Fp2 load(const uint32_t *p) { return Fp2{F::load(p), F::load(p + P::N)}; }
+    B200_DEV void store(uint32_t *p) const {
+        c0.store(p);
+        c1.store(p + P::N);
+    }
+};
+
+}  // namespace b200msm

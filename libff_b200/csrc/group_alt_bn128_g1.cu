@@ -1,0 +1,7 @@
+// Instantiates the device pipelines for alt_bn128_g1 (one translation unit per group keeps the
+// fully unrolled limb code of each field compiling in parallel).
+#include "engine_impl.cuh"
+
+namespace b200msm {
+const GroupOps *ops_alt_bn128_g1() { return make_ops<AltBn128G1>(); }
+}  // namespace b200msm

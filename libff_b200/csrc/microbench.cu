@@ -1,0 +1,134 @@
+// Integer-pipe microbenchmarks for the MSM roofline: MEASURED_PEAKS.json has no
+// integer peak, so the denominators used by bench.py are measured here.
+//   imad32     independent 32-bit IMAD chains (mad.lo.u32)
+//   imadwide   independent IMAD.WIDE.U32 chains (mad.wide.u32, 64-bit accumulate)
+//   mont<N>    back-to-back Montgomery products of the field code itself (fp.cuh)
+// Prints one JSON object.  Usage: microbench [iters]
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstdlib>
+
+#include "fp.cuh"
+
+using namespace b200msm;
+
+#define CK(x)                                                                      \
+    do {                                                                           \
+        cudaError_t e = (x);                                                       \
+        if (e != cudaSuccess) {                                                    \
+            fprintf(stderr, "%s: %s\n", #x, cudaGetErrorString(e));                \
+            exit(1);                                                               \
+        }                                                                          \
+    } while (0)
+
+constexpr int ILP = 8;
+
+__global__ void k_imad32(uint32_t *out, uint32_t seed, int iters) {
+    uint32_t a[ILP], m = seed | 1u, x = threadIdx.x + 3;
+#pragma unroll
+    for (int i = 0; i < ILP; i++) a[i] = seed + i + threadIdx.x;
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int u = 0; u < 8; u++)
+#pragma unroll
+            for (int i = 0; i < ILP; i++)
+                asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a[i]) : "r"(m), "r"(x));
+    }
+    uint32_t s = 0;
+#pragma unroll
+    for (int i = 0; i < ILP; i++) s ^= a[i];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+__global__ void k_imadwide(uint64_t *out, uint32_t seed, int iters) {
+    uint64_t a[ILP];
+    uint32_t m = seed | 1u, x = threadIdx.x + 3;
+#pragma unroll
+    for (int i = 0; i < ILP; i++) a[i] = seed + i + threadIdx.x;
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int u = 0; u < 8; u++)
+#pragma unroll
+            for (int i = 0; i < ILP; i++)
+                asm volatile("{ .reg .u32 lo; cvt.u32.u64 lo, %0; mad.wide.u32 %0, lo, %1, %0; }"
+                             : "+l"(a[i])
+                             : "r"(m));
+    }
+    uint64_t s = 0;
+#pragma unroll
+    for (int i = 0; i < ILP; i++) s ^= a[i];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+template <class P>
+__global__ void k_mont(uint32_t *out, uint32_t seed, int iters) {
+    using F = Fp<P>;
+    F a = F::one(), b = F::one();
+    a.v[0] ^= seed + threadIdx.x;
+    b.v[1] ^= seed * 3 + blockIdx.x;
+    a.v[P::N - 1] &= 0x0fffffff;
+    b.v[P::N - 1] &= 0x0fffffff;
+#pragma unroll 1
+    for (int it = 0; it < iters; it++) {
+        a = F::mul_inline(a, b);
+        b = F::mul_inline(b, a);
+    }
+    uint32_t s = 0;
+#pragma unroll
+    for (int i = 0; i < P::N; i++) s ^= a.v[i] ^ b.v[i];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+template <class K>
+static float time_ms(K launch) {
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0));
+    CK(cudaEventCreate(&e1));
+    launch();
+    CK(cudaDeviceSynchronize());
+    float best = 1e30f;
+    for (int r = 0; r < 3; r++) {
+        CK(cudaEventRecord(e0));
+        launch();
+        CK(cudaEventRecord(e1));
+        CK(cudaEventSynchronize(e1));
+        float ms;
+        CK(cudaEventElapsedTime(&ms, e0, e1));
+        if (ms < best) best = ms;
+    }
+    return best;
+}
+
+int main(int argc, char **argv) {
+    int iters = argc > 1 ? atoi(argv[1]) : 2000;
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, 0));
+    const int sms = prop.multiProcessorCount;
+    void *out;
+    CK(cudaMalloc(&out, (size_t)sms * 8 * 1024 * 8));
+    printf("{\"gpu\": \"%s\", \"sms\": %d", prop.name, sms);
+    for (int warps : {4, 8, 16, 32}) {
+        int threads = warps * 32 > 1024 ? 1024 : warps * 32;
+        int blocks = sms * (warps * 32 / threads);
+        double ops = (double)blocks * threads * iters * 8.0 * ILP;
+        float ms = time_ms([&] { k_imad32<<<blocks, threads>>>((uint32_t *)out, 12345, iters); });
+        printf(", \"imad32_w%d_Tops\": %.3f", warps, ops / ms * 1e-9);
+        ms = time_ms([&] { k_imadwide<<<blocks, threads>>>((uint64_t *)out, 12345, iters); });
+        printf(", \"imadwide_w%d_Tops\": %.3f", warps, ops / ms * 1e-9);
+    }
+    for (int wps : {4, 8, 12, 16}) {  // resident warps per SM
+        int blocks = sms * wps / 4;
+        double muls = (double)blocks * 128 * iters * 2.0;
+        float ms = time_ms([&] { k_mont<AltBn128FqParams><<<blocks, 128>>>((uint32_t *)out, 7, iters); });
+        printf(", \"mont8_w%d_Gmul\": %.2f", wps, muls / ms * 1e-6);
+        ms = time_ms([&] { k_mont<Bls12377FqParams><<<blocks, 128>>>((uint32_t *)out, 7, iters / 2); });
+        printf(", \"mont12_w%d_Gmul\": %.2f", wps, muls / 2 / ms * 1e-6);
+        if (wps <= 8) {
+            ms = time_ms([&] { k_mont<Bw6761FqParams><<<blocks, 128>>>((uint32_t *)out, 7, iters / 8); });
+            printf(", \"mont24_w%d_Gmul\": %.2f", wps, muls / 8 / ms * 1e-6);
+        }
+    }
+    printf("}\n");
+    return 0;
+}

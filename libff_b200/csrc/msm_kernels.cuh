@@ -1,0 +1,317 @@
+// MSM kernels (bucket method) -- device replacement for multi_exp_method_BDLO12 /
+// BDLO12_signed (libff/algebra/scalar_multiplication/multiexp.tcc:276-381, 507-633).
+//
+// Pipeline (one launch each, all windows at once):
+//   k_digits        scalars: Montgomery -> plain (fp.tcc:270-281) -> signed c-bit digits
+//                   (field_utils.tcc:167-239 restated as a single carry pass) + bucket histogram
+//   k_scan          exclusive prefix sum of the histogram -> bucket offsets
+//   k_scatter       counting-sort scatter of (bucket, point index | sign) pairs
+//   k_accum_first   balanced segmented accumulation: every thread sums SEG consecutive sorted
+//                   entries with mixed additions (multiexp.tcc:319-345 / :45-81); sums of buckets
+//                   that begin inside the segment are stored, the leading partial becomes a carry
+//   k_accum_carry   same on the (already sorted) carry list with full additions, until no carries
+//   k_bucket_reduce running sums over chunks of buckets (multiexp.tcc:90-125, 354-376)
+//   k_window_reduce per-window total
+//   k_final         Horner over windows (multiexp.tcc:309-314) -> reference coordinates
+// Any bucket-method schedule yields the same group element; parity is on the affine result.
+#pragma once
+#include "curves.cuh"
+
+namespace b200msm {
+
+struct Entry {           // one sorted item: global bucket id, point index with the sign in bit 31
+    uint32_t bucket;
+    uint32_t idx;
+};
+
+// ------------------------------------------------------------------------------------------
+// bases: reference layout -> device affine (x, y); infinity -> (0, 0) + flag
+template <class C>
+__global__ void k_ingest_special(const uint32_t *__restrict__ raw, uint32_t *__restrict__ aff,
+                                 uint8_t *__restrict__ inf_flag, uint32_t n) {
+    using R = Raw<C>;
+    using F = typename C::Fq;
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    F X, Y, Z;
+    R::load(raw + (size_t)i * R::PW, X, Y, Z);
+    bool inf = R::is_inf(X, Z);
+    Affine<F> a{inf ? F::zero() : X, inf ? F::zero() : Y};
+    a.store(aff + (size_t)i * R::AW);
+    inf_flag[i] = inf;
+}
+
+// ------------------------------------------------------------------------------------------
+// scalars -> signed digits + histogram.  digits[w * n + i] in [-2^(c-1), 2^(c-1)]
+template <class C>
+__global__ void k_digits(const uint32_t *__restrict__ scalars, const uint8_t *__restrict__ inf_flag,
+                         int32_t *__restrict__ digits, uint32_t *__restrict__ hist, uint32_t n,
+                         int c, int W) {
+    using Fr = typename C::Fr;
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Fr s = Fr::from_mont(Fr::load(scalars + (size_t)i * Fr::N));
+    bool skip = inf_flag != nullptr && inf_flag[i];
+    const uint32_t mask = (1u << c) - 1, half = 1u << (c - 1);
+    uint32_t carry = 0;
+    for (int w = 0; w < W; w++) {
+        uint32_t d = (s.v[0] & mask) + carry;
+        carry = d > half;
+        int32_t sd = (int32_t)d - (int32_t)(carry << c);
+        if (skip) sd = 0;
+        digits[(size_t)w * n + i] = sd;
+        if (sd != 0) atomicAdd(&hist[(size_t)w * half + (sd < 0 ? -sd : sd) - 1], 1u);
+#pragma unroll
+        for (int k = 0; k < Fr::N - 1; k++) s.v[k] = __funnelshift_r(s.v[k], s.v[k + 1], c);
+        s.v[Fr::N - 1] >>= c;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// exclusive scan of m counters (single block); offsets has m + 1 entries, cursor m
+static __global__ void k_scan(const uint32_t *__restrict__ hist, uint32_t *__restrict__ offsets,
+                       uint32_t *__restrict__ cursor, uint32_t m) {
+    __shared__ uint32_t part[1024];
+    const uint32_t t = threadIdx.x, nt = blockDim.x;
+    const uint32_t per = (m + nt - 1) / nt;
+    const uint32_t lo = min(m, t * per), hi = min(m, lo + per);
+    uint32_t s = 0;
+    for (uint32_t k = lo; k < hi; k++) s += hist[k];
+    part[t] = s;
+    __syncthreads();
+    for (uint32_t d = 1; d < nt; d <<= 1) {
+        uint32_t v = t >= d ? part[t - d] : 0;
+        __syncthreads();
+        part[t] += v;
+        __syncthreads();
+    }
+    uint32_t run = part[t] - s;
+    for (uint32_t k = lo; k < hi; k++) {
+        offsets[k] = run;
+        cursor[k] = run;
+        run += hist[k];
+    }
+    if (t == nt - 1) offsets[m] = part[t];
+}
+
+// ------------------------------------------------------------------------------------------
+template <class C>
+__global__ void k_scatter(const int32_t *__restrict__ digits, uint32_t *__restrict__ cursor,
+                          Entry *__restrict__ sorted, uint32_t n, int c) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t w = blockIdx.y;
+    if (i >= n) return;
+    int32_t d = digits[(size_t)w * n + i];
+    if (d == 0) return;
+    uint32_t b = (w << (c - 1)) + (uint32_t)(d < 0 ? -d : d) - 1;
+    uint32_t pos = atomicAdd(&cursor[b], 1u);
+    sorted[pos] = Entry{b, i | (d < 0 ? 0x80000000u : 0u)};
+}
+
+// ------------------------------------------------------------------------------------------
+// First accumulation round: thread t owns sorted[t*SEG, (t+1)*SEG).
+template <class C, int SEG>
+__global__ void __launch_bounds__(128)
+    k_accum_first(const Entry *__restrict__ sorted, uint32_t total,
+                  const uint32_t *__restrict__ aff, uint32_t *__restrict__ bucket_acc,
+                  uint32_t *__restrict__ carry_key, uint32_t *__restrict__ carry_pt) {
+    using R = Raw<C>;
+    using F = typename C::Fq;
+    using X = XYZZ<F>;
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t start64 = (uint64_t)t * SEG;
+    if (start64 >= total) return;
+    const uint32_t start = (uint32_t)start64;
+    const uint32_t end = (uint32_t)min((uint64_t)total, start64 + SEG);
+
+    Entry e = sorted[start];
+    uint32_t cur = e.bucket;
+    bool head_carry = start > 0 && sorted[start - 1].bucket == cur;
+    carry_key[t] = cur;
+    bool carried = false;
+    X acc = X::inf();
+    Affine<F> p = Affine<F>::load(aff + (size_t)(e.idx & 0x7fffffffu) * R::AW);
+    for (uint32_t pos = start; pos < end; pos++) {
+        const Entry ecur = e;
+        const Affine<F> pcur = p;
+        if (pos + 1 < end) {  // prefetch the next entry and point
+            e = sorted[pos + 1];
+            p = Affine<F>::load(aff + (size_t)(e.idx & 0x7fffffffu) * R::AW);
+        }
+        if (ecur.bucket != cur) {
+            if (head_carry && !carried) {
+                acc.store(carry_pt + (size_t)t * R::XW);
+                carried = true;
+            } else {
+                acc.store(bucket_acc + (size_t)cur * R::XW);
+            }
+            head_carry = false;
+            cur = ecur.bucket;
+            acc = X::inf();
+        }
+        X::madd(acc, pcur.x, F::cneg(pcur.y, (ecur.idx >> 31) != 0));
+    }
+    if (head_carry && !carried) {
+        acc.store(carry_pt + (size_t)t * R::XW);
+        carried = true;
+    } else {
+        acc.store(bucket_acc + (size_t)cur * R::XW);
+    }
+    if (!carried) X::inf().store(carry_pt + (size_t)t * R::XW);
+}
+
+// Later rounds: the carry list (keys ascending, one XYZZ point each) is reduced the same way with
+// full additions; sums of runs that begin a bucket in this list are added into bucket_acc.
+template <class C, int SEG>
+__global__ void __launch_bounds__(128)
+    k_accum_carry(const uint32_t *__restrict__ keys, const uint32_t *__restrict__ pts,
+                  uint32_t total, uint32_t *__restrict__ bucket_acc,
+                  uint32_t *__restrict__ carry_key, uint32_t *__restrict__ carry_pt) {
+    using R = Raw<C>;
+    using F = typename C::Fq;
+    using X = XYZZ<F>;
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t start64 = (uint64_t)t * SEG;
+    if (start64 >= total) return;
+    const uint32_t start = (uint32_t)start64;
+    const uint32_t end = (uint32_t)min((uint64_t)total, start64 + SEG);
+    uint32_t cur = keys[start];
+    bool head_carry = start > 0 && keys[start - 1] == cur;
+    bool carried = false;
+    carry_key[t] = cur;
+    X acc = X::inf();
+    for (uint32_t pos = start; pos <= end; pos++) {
+        uint32_t k = pos < end ? keys[pos] : 0xffffffffu;
+        if (k != cur) {
+            if (head_carry && !carried) {
+                acc.store(carry_pt + (size_t)t * R::XW);
+                carried = true;
+            } else if (!acc.is_inf()) {
+                X b = X::load(bucket_acc + (size_t)cur * R::XW);
+                X::add(b, acc);
+                b.store(bucket_acc + (size_t)cur * R::XW);
+            }
+            head_carry = false;
+            cur = k;
+            acc = X::inf();
+        }
+        if (pos < end) {
+            X q = X::load(pts + (size_t)pos * R::XW);
+            X::add(acc, q);
+        }
+    }
+    if (!carried) X::inf().store(carry_pt + (size_t)t * R::XW);
+}
+
+// ------------------------------------------------------------------------------------------
+// k * p for a small non-negative k (double-and-add, MSB first)
+template <class F>
+__device__ __noinline__ XYZZ<F> small_mul(const XYZZ<F> &p, uint32_t k) {
+    XYZZ<F> r = XYZZ<F>::inf();
+    if (k == 0 || p.is_inf()) return r;
+    for (int bit = 31 - __clz(k); bit >= 0; bit--) {
+        r = XYZZ<F>::dbl(r);
+        if ((k >> bit) & 1) XYZZ<F>::add(r, p);
+    }
+    return r;
+}
+
+// Thread (w, j) reduces buckets [j*K, (j+1)*K) of window w:
+//   sum_{b} (j*K + b + 1) * bucket[b]  =  (running sums)  +  (j*K) * (chunk total)
+// B = buckets per window; grid.x covers B/K chunks, grid.y = windows.
+template <class C>
+__global__ void __launch_bounds__(64)
+    k_bucket_reduce(const uint32_t *__restrict__ bucket_acc, const uint32_t *__restrict__ hist,
+                    uint32_t B, uint32_t K, uint32_t *__restrict__ chunk_sums) {
+    using R = Raw<C>;
+    using F = typename C::Fq;
+    using X = XYZZ<F>;
+    const uint32_t chunks = (B + K - 1) / K;
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t w = blockIdx.y;
+    if (j >= chunks) return;
+    const uint32_t lo = j * K, hi = min(B, lo + K);
+    X running = X::inf(), acc = X::inf();
+    for (uint32_t b = hi; b-- > lo;) {
+        const size_t g = (size_t)w * B + b;
+        if (hist[g] != 0) {  // empty buckets were never written
+            X q = X::load(bucket_acc + g * R::XW);
+            X::add(running, q);
+        }
+        X::add(acc, running);
+    }
+    X off = small_mul<F>(running, lo);
+    X::add(acc, off);
+    acc.store(chunk_sums + ((size_t)w * chunks + j) * R::XW);
+}
+
+// One block per window: total of its chunk sums (strided per thread, then a shared-memory tree).
+template <class C, int THREADS>
+__global__ void __launch_bounds__(THREADS)
+    k_window_reduce(const uint32_t *__restrict__ chunk_sums, uint32_t chunks,
+                    uint32_t *__restrict__ window_sums) {
+    using R = Raw<C>;
+    using F = typename C::Fq;
+    using X = XYZZ<F>;
+    extern __shared__ uint32_t smem[];
+    const uint32_t w = blockIdx.x, t = threadIdx.x;
+    X acc = X::inf();
+    for (uint32_t j = t; j < chunks; j += THREADS) {
+        X q = X::load(chunk_sums + ((size_t)w * chunks + j) * R::XW);
+        X::add(acc, q);
+    }
+    acc.store(smem + (size_t)t * R::XW);
+    __syncthreads();
+    for (uint32_t d = THREADS / 2; d > 0; d >>= 1) {
+        if (t < d) {
+            X q = X::load(smem + (size_t)(t + d) * R::XW);
+            X::add(acc, q);
+            acc.store(smem + (size_t)t * R::XW);
+        }
+        __syncthreads();
+    }
+    if (t == 0) acc.store(window_sums + (size_t)w * R::XW);
+}
+
+// result = sum_w 2^(w c) window_sums[w]  (+ optional previous partial), written both as XYZZ and
+// in the reference's coordinate system.
+template <class C>
+__global__ void k_final(const uint32_t *__restrict__ window_sums, int W, int c,
+                        uint32_t *__restrict__ out_raw) {
+    using R = Raw<C>;
+    using F = typename C::Fq;
+    using X = XYZZ<F>;
+    if (blockIdx.x != 0 || threadIdx.x != 0) return;
+    X r = X::inf();
+    for (int w = W - 1; w >= 0; w--) {
+        if (!r.is_inf())
+            for (int k = 0; k < c; k++) r = X::dbl(r);
+        X q = X::load(window_sums + (size_t)w * R::XW);
+        X::add(r, q);
+    }
+    F Xo, Yo, Zo;
+    R::from_xyzz(r, Xo, Yo, Zo);
+    R::store(out_raw, Xo, Yo, Zo);
+}
+
+// Sum of `count` reference-layout group elements (partials of the GPU shards, multiexp.tcc:681-685)
+template <class C>
+__global__ void k_sum_raw(const uint32_t *__restrict__ raw, uint32_t count,
+                          uint32_t *__restrict__ out_raw) {
+    using R = Raw<C>;
+    using F = typename C::Fq;
+    using X = XYZZ<F>;
+    if (blockIdx.x != 0 || threadIdx.x != 0) return;
+    X r = X::inf();
+    for (uint32_t i = 0; i < count; i++) {
+        F Xi, Yi, Zi;
+        R::load(raw + (size_t)i * R::PW, Xi, Yi, Zi);
+        X q = R::to_xyzz(Xi, Yi, Zi);
+        X::add(r, q);
+    }
+    F Xo, Yo, Zo;
+    R::from_xyzz(r, Xo, Yo, Zo);
+    R::store(out_raw, Xo, Yo, Zo);
+}
+
+}  // namespace b200msm
