@@ -99,6 +99,15 @@ bool b200msm_batch_exp(uint32_t group, size_t scalar_bits, size_t window,
                        const void *scalars, size_t scalars_bytes, size_t n, void *out,
                        size_t out_bytes);
 
+/* Element-wise leaves of the path, for parity tests (n elements each, same layout as above):
+ * op 0..5 coordinate field add, sub, mul, sqr, neg, inverse (Fp_model, fields/fp.tcc:50-727;
+ * Fp2_model for alt_bn128 G2, fields/fp2.tcc:79-168); 6 scalar field Montgomery -> plain
+ * (as_bigint, fp.tcc:270-281); 7 scalar field mul; 10 group add, 11 dbl, 12 mixed add (b special),
+ * 13 negation (e.g. alt_bn128_g1.cpp:139-326).  `b` may be NULL for unary ops.  bytes is the
+ * size of each of a, b, out. */
+bool b200msm_debug_op(uint32_t group, uint32_t op, const void *a, const void *b, void *out,
+                      size_t bytes, size_t n);
+
 /* Tuning and measurement (not part of the reference surface).
  * option: "window_bits" (0 = automatic), "segment" (entries per thread of the accumulation). */
 bool b200msm_set_option(const char *name, int64_t value);

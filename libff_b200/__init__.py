@@ -41,7 +41,7 @@ ABI_SYMBOLS = [
     "b200msm_init", "b200msm_shutdown", "b200msm_last_error", "b200msm_group_bytes",
     "b200msm_scalar_bytes", "b200msm_multi_exp", "b200msm_bases_upload",
     "b200msm_scalars_upload", "b200msm_multi_exp_resident", "b200msm_release", "b200msm_sum",
-    "b200msm_batch_to_special", "b200msm_batch_exp", "b200msm_set_option",
+    "b200msm_batch_to_special", "b200msm_batch_exp", "b200msm_debug_op", "b200msm_set_option",
     "b200msm_last_timings", "b200msm_timing_name", "b200msm_launch_count", "b200msm_window_bits",
 ]
 
@@ -85,6 +85,7 @@ def load():
         "b200msm_sum": (C.c_bool, [u32, vp, sz, sz, vp, sz]),
         "b200msm_batch_to_special": (C.c_bool, [u32, vp, sz, sz]),
         "b200msm_batch_exp": (C.c_bool, [u32, sz, sz, C.POINTER(vp), sz, sz, vp, sz, sz, vp, sz]),
+        "b200msm_debug_op": (C.c_bool, [u32, u32, vp, vp, vp, sz, sz]),
         "b200msm_set_option": (C.c_bool, [C.c_char_p, i64]),
         "b200msm_last_timings": (sz, [C.POINTER(C.c_float), sz]),
         "b200msm_timing_name": (C.c_char_p, [sz]),
@@ -219,6 +220,28 @@ def batch_to_special(group: int, points) -> np.ndarray:
     if not load().b200msm_batch_to_special(group, _ptr(p), p.nbytes, n):
         _fail("b200msm_batch_to_special")
     return p
+
+
+# element-wise leaves (b200msm_debug_op)
+FQ_ADD, FQ_SUB, FQ_MUL, FQ_SQR, FQ_NEG, FQ_INV, FR_FROM_MONT, FR_MUL = range(8)
+G_ADD, G_DBL, G_MADD, G_NEG = 10, 11, 12, 13
+
+
+def debug_op(group: int, op: int, a, b=None) -> np.ndarray:
+    """One field / group operation per element on the device (parity tests of the leaves)."""
+    _ensure_init()
+    a = _as_u64(a, "a")
+    n = a.shape[0]
+    out = np.zeros_like(a)
+    bp = None
+    if b is not None:
+        b = _as_u64(b, "b")
+        if b.shape != a.shape:
+            raise B200MsmError("debug_op: operand shapes differ")
+        bp = _ptr(b)
+    if not load().b200msm_debug_op(group, op, _ptr(a), bp, _ptr(out), a.nbytes, n):
+        _fail("b200msm_debug_op")
+    return out
 
 
 def batch_exp(group: int, scalar_size: int, window: int, table: Sequence, scalars) -> np.ndarray:

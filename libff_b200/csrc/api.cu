@@ -353,6 +353,28 @@ bool b200msm_batch_exp(uint32_t group, size_t scalar_bits, size_t window,
     return true;
 }
 
+bool b200msm_debug_op(uint32_t group, uint32_t op, const void *a, const void *b, void *out,
+                      size_t bytes, size_t n) {
+    std::lock_guard<std::mutex> lk(g_mutex);
+    const GroupOps *ops = checked_ops(group);
+    if (!ops || !ready()) return false;
+    const size_t eb = ops->debug_elem_bytes((int)op);
+    if (eb == 0) return set_error("debug_op: unknown op %u", op), false;
+    if (bytes != n * eb || (n > 0 && (!a || !out))) return set_error("debug_op: size mismatch"), false;
+    if (n == 0) return true;
+    Ctx &ctx = *g_ctx;
+    void *d_a, *d_b, *d_out;
+    if (!ctx.reserve(SL_RAW, bytes, &d_a)) return false;
+    if (!ctx.reserve(SL_AFF, bytes, &d_b)) return false;
+    if (!ctx.reserve(SL_BEXP_OUT, bytes, &d_out)) return false;
+    B200_CUDA(cudaMemcpyAsync(d_a, a, bytes, cudaMemcpyHostToDevice, ctx.stream));
+    if (b) B200_CUDA(cudaMemcpyAsync(d_b, b, bytes, cudaMemcpyHostToDevice, ctx.stream));
+    if (!ops->debug_op(ctx, (int)op, d_a, d_b, d_out, n)) return false;
+    B200_CUDA(cudaStreamSynchronize(ctx.stream));
+    B200_CUDA(cudaMemcpy(out, d_out, bytes, cudaMemcpyDeviceToHost));
+    return true;
+}
+
 bool b200msm_set_option(const char *name, int64_t value) {
     std::lock_guard<std::mutex> lk(g_mutex);
     if (!g_ctx) return set_error("set_option before init"), false;

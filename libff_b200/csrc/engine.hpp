@@ -104,6 +104,9 @@ struct GroupOps {
     bool (*batch_exp)(Ctx &, const void *d_table_raw, size_t rows, size_t row_len, int window,
                       const void *d_scalars, size_t n, void *d_out);
     uint32_t (*window_bits)(const Ctx &, size_t n);
+    // element-wise leaf operation (debug_kernels.cuh); returns bytes per element via elem_bytes
+    bool (*debug_op)(Ctx &, int op, const void *d_a, const void *d_b, void *d_out, size_t n);
+    size_t (*debug_elem_bytes)(int op);
 };
 
 const GroupOps *ops_alt_bn128_g1();

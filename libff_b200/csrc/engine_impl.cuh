@@ -3,6 +3,7 @@
 #include <algorithm>
 
 #include "batch_kernels.cuh"
+#include "debug_kernels.cuh"
 #include "engine.hpp"
 #include "msm_kernels.cuh"
 
@@ -261,6 +262,24 @@ uint32_t window_bits_impl(const Ctx &ctx, size_t n) {
 }
 
 template <class C>
+size_t debug_elem_bytes_impl(int op) {
+    using R = Raw<C>;
+    if (op <= DBG_FQ_INV) return (size_t)R::CW * 4;
+    if (op == DBG_FR_FROM_MONT || op == DBG_FR_MUL) return (size_t)R::SW * 4;
+    if (op >= DBG_G_ADD && op <= DBG_G_NEG) return (size_t)R::PW * 4;
+    return 0;
+}
+
+template <class C>
+bool debug_op_impl(Ctx &ctx, int op, const void *d_a, const void *d_b, void *d_out, size_t n) {
+    if (n == 0) return true;
+    k_debug_op<C><<<cdiv(n, 64), 64, 0, ctx.stream>>>(op, (const uint32_t *)d_a, (const uint32_t *)d_b,
+                                                       (uint32_t *)d_out, (uint32_t)n);
+    B200_LAUNCH_CHECK(ctx);
+    return true;
+}
+
+template <class C>
 const GroupOps *make_ops() {
     using R = Raw<C>;
     static const GroupOps ops = {(uint32_t)C::ID,
@@ -273,7 +292,9 @@ const GroupOps *make_ops() {
                                  &sum_impl<C>,
                                  &to_special_impl<C>,
                                  &batch_exp_impl<C>,
-                                 &window_bits_impl<C>};
+                                 &window_bits_impl<C>,
+                                 &debug_op_impl<C>,
+                                 &debug_elem_bytes_impl<C>};
     return &ops;
 }
 

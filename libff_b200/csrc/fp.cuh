@@ -34,20 +34,20 @@ template <int N>
 B200_DEV void row_set(uint32_t *acc, const uint32_t *a, uint32_t bi) {
 #pragma unroll
     for (int j = 0; j < N; j += 2) {
-        asm("mul.lo.u32 %0, %1, %2;" : "=r"(acc[j]) : "r"(a[j]), "r"(bi));
-        asm("mul.hi.u32 %0, %1, %2;" : "=r"(acc[j + 1]) : "r"(a[j]), "r"(bi));
+        asm volatile("mul.lo.u32 %0, %1, %2;" : "=r"(acc[j]) : "r"(a[j]), "r"(bi));
+        asm volatile("mul.hi.u32 %0, %1, %2;" : "=r"(acc[j + 1]) : "r"(a[j]), "r"(bi));
     }
 }
 
 // acc[j], acc[j+1] += a[j] * bi for even j < N, one carry chain; carry-out stays in CC
 template <int N>
 B200_DEV void row_acc(uint32_t *acc, const uint32_t *a, uint32_t bi) {
-    asm("mad.lo.cc.u32 %0, %1, %2, %0;" : "+r"(acc[0]) : "r"(a[0]), "r"(bi));
-    asm("madc.hi.cc.u32 %0, %1, %2, %0;" : "+r"(acc[1]) : "r"(a[0]), "r"(bi));
+    asm volatile("mad.lo.cc.u32 %0, %1, %2, %0;" : "+r"(acc[0]) : "r"(a[0]), "r"(bi));
+    asm volatile("madc.hi.cc.u32 %0, %1, %2, %0;" : "+r"(acc[1]) : "r"(a[0]), "r"(bi));
 #pragma unroll
     for (int j = 2; j < N; j += 2) {
-        asm("madc.lo.cc.u32 %0, %1, %2, %0;" : "+r"(acc[j]) : "r"(a[j]), "r"(bi));
-        asm("madc.hi.cc.u32 %0, %1, %2, %0;" : "+r"(acc[j + 1]) : "r"(a[j]), "r"(bi));
+        asm volatile("madc.lo.cc.u32 %0, %1, %2, %0;" : "+r"(acc[j]) : "r"(a[j]), "r"(bi));
+        asm volatile("madc.hi.cc.u32 %0, %1, %2, %0;" : "+r"(acc[j + 1]) : "r"(a[j]), "r"(bi));
     }
 }
 
@@ -57,13 +57,13 @@ template <int N>
 B200_DEV void row_acc_shift(uint32_t *acc, const uint32_t *a, uint32_t bi) {
 #pragma unroll
     for (int j = 0; j < N - 2; j += 2) {
-        asm("madc.lo.cc.u32 %0, %1, %2, %3;" : "=r"(acc[j]) : "r"(a[j]), "r"(bi), "r"(acc[j + 2]));
-        asm("madc.hi.cc.u32 %0, %1, %2, %3;"
+        asm volatile("madc.lo.cc.u32 %0, %1, %2, %3;" : "=r"(acc[j]) : "r"(a[j]), "r"(bi), "r"(acc[j + 2]));
+        asm volatile("madc.hi.cc.u32 %0, %1, %2, %3;"
             : "=r"(acc[j + 1])
             : "r"(a[j]), "r"(bi), "r"(acc[j + 3]));
     }
-    asm("madc.lo.cc.u32 %0, %1, %2, 0;" : "=r"(acc[N - 2]) : "r"(a[N - 2]), "r"(bi));
-    asm("madc.hi.u32 %0, %1, %2, 0;" : "=r"(acc[N - 1]) : "r"(a[N - 2]), "r"(bi));
+    asm volatile("madc.lo.cc.u32 %0, %1, %2, 0;" : "=r"(acc[N - 2]) : "r"(a[N - 2]), "r"(bi));
+    asm volatile("madc.hi.u32 %0, %1, %2, 0;" : "=r"(acc[N - 1]) : "r"(a[N - 2]), "r"(bi));
 }
 
 }  // namespace limb
@@ -102,12 +102,12 @@ struct Fp {
     // r = a - p if a >= p else a     (a < 2p)
     B200_DEV static Fp reduce_once(const Fp &a) {
         Fp s;
-        asm("sub.cc.u32 %0, %1, %2;" : "=r"(s.v[0]) : "r"(a.v[0]), "r"(P::mod(0)));
+        asm volatile("sub.cc.u32 %0, %1, %2;" : "=r"(s.v[0]) : "r"(a.v[0]), "r"(P::mod(0)));
 #pragma unroll
         for (int i = 1; i < N; i++)
-            asm("subc.cc.u32 %0, %1, %2;" : "=r"(s.v[i]) : "r"(a.v[i]), "r"(P::mod(i)));
+            asm volatile("subc.cc.u32 %0, %1, %2;" : "=r"(s.v[i]) : "r"(a.v[i]), "r"(P::mod(i)));
         uint32_t borrow;
-        asm("subc.u32 %0, 0, 0;" : "=r"(borrow));
+        asm volatile("subc.u32 %0, 0, 0;" : "=r"(borrow));
         Fp r;
 #pragma unroll
         for (int i = 0; i < N; i++) r.v[i] = borrow ? a.v[i] : s.v[i];
@@ -117,11 +117,11 @@ struct Fp {
     // fp.tcc:350-465 -- top limb has spare bits, so a + b never carries out of N limbs
     B200_DEV static Fp add(const Fp &a, const Fp &b) {
         Fp t;
-        asm("add.cc.u32 %0, %1, %2;" : "=r"(t.v[0]) : "r"(a.v[0]), "r"(b.v[0]));
+        asm volatile("add.cc.u32 %0, %1, %2;" : "=r"(t.v[0]) : "r"(a.v[0]), "r"(b.v[0]));
 #pragma unroll
         for (int i = 1; i < N - 1; i++)
-            asm("addc.cc.u32 %0, %1, %2;" : "=r"(t.v[i]) : "r"(a.v[i]), "r"(b.v[i]));
-        asm("addc.u32 %0, %1, %2;" : "=r"(t.v[N - 1]) : "r"(a.v[N - 1]), "r"(b.v[N - 1]));
+            asm volatile("addc.cc.u32 %0, %1, %2;" : "=r"(t.v[i]) : "r"(a.v[i]), "r"(b.v[i]));
+        asm volatile("addc.u32 %0, %1, %2;" : "=r"(t.v[N - 1]) : "r"(a.v[N - 1]), "r"(b.v[N - 1]));
         return reduce_once(t);
     }
     B200_DEV static Fp dbl(const Fp &a) { return add(a, a); }
@@ -129,18 +129,18 @@ struct Fp {
     // fp.tcc:467-547
     B200_DEV static Fp sub(const Fp &a, const Fp &b) {
         Fp t;
-        asm("sub.cc.u32 %0, %1, %2;" : "=r"(t.v[0]) : "r"(a.v[0]), "r"(b.v[0]));
+        asm volatile("sub.cc.u32 %0, %1, %2;" : "=r"(t.v[0]) : "r"(a.v[0]), "r"(b.v[0]));
 #pragma unroll
         for (int i = 1; i < N; i++)
-            asm("subc.cc.u32 %0, %1, %2;" : "=r"(t.v[i]) : "r"(a.v[i]), "r"(b.v[i]));
+            asm volatile("subc.cc.u32 %0, %1, %2;" : "=r"(t.v[i]) : "r"(a.v[i]), "r"(b.v[i]));
         uint32_t borrow;
-        asm("subc.u32 %0, 0, 0;" : "=r"(borrow));  // 0 or 0xffffffff
+        asm volatile("subc.u32 %0, 0, 0;" : "=r"(borrow));  // 0 or 0xffffffff
         Fp r;
-        asm("add.cc.u32 %0, %1, %2;" : "=r"(r.v[0]) : "r"(t.v[0]), "r"(P::mod(0) & borrow));
+        asm volatile("add.cc.u32 %0, %1, %2;" : "=r"(r.v[0]) : "r"(t.v[0]), "r"(P::mod(0) & borrow));
 #pragma unroll
         for (int i = 1; i < N - 1; i++)
-            asm("addc.cc.u32 %0, %1, %2;" : "=r"(r.v[i]) : "r"(t.v[i]), "r"(P::mod(i) & borrow));
-        asm("addc.u32 %0, %1, %2;"
+            asm volatile("addc.cc.u32 %0, %1, %2;" : "=r"(r.v[i]) : "r"(t.v[i]), "r"(P::mod(i) & borrow));
+        asm volatile("addc.u32 %0, %1, %2;"
             : "=r"(r.v[N - 1])
             : "r"(t.v[N - 1]), "r"(P::mod(N - 1) & borrow));
         return r;
@@ -150,11 +150,11 @@ struct Fp {
     B200_DEV static Fp neg(const Fp &a) {
         uint32_t nz = a.is_zero() ? 0u : 0xffffffffu;
         Fp r;
-        asm("sub.cc.u32 %0, %1, %2;" : "=r"(r.v[0]) : "r"(P::mod(0) & nz), "r"(a.v[0]));
+        asm volatile("sub.cc.u32 %0, %1, %2;" : "=r"(r.v[0]) : "r"(P::mod(0) & nz), "r"(a.v[0]));
 #pragma unroll
         for (int i = 1; i < N - 1; i++)
-            asm("subc.cc.u32 %0, %1, %2;" : "=r"(r.v[i]) : "r"(P::mod(i) & nz), "r"(a.v[i]));
-        asm("subc.u32 %0, %1, %2;" : "=r"(r.v[N - 1]) : "r"(P::mod(N - 1) & nz), "r"(a.v[N - 1]));
+            asm volatile("subc.cc.u32 %0, %1, %2;" : "=r"(r.v[i]) : "r"(P::mod(i) & nz), "r"(a.v[i]));
+        asm volatile("subc.u32 %0, %1, %2;" : "=r"(r.v[N - 1]) : "r"(P::mod(N - 1) & nz), "r"(a.v[N - 1]));
         return r;
     }
     B200_DEV static Fp cneg(const Fp &a, bool flag) {
@@ -182,17 +182,17 @@ struct Fp {
             limb::row_set<N>(O, a + 1, bi);
             limb::row_set<N>(E, a, bi);
         } else {
-            asm("add.cc.u32 %0, %0, %1;" : "+r"(E[0]) : "r"(O[1]));
+            asm volatile("add.cc.u32 %0, %0, %1;" : "+r"(E[0]) : "r"(O[1]));
             limb::row_acc_shift<N>(O, a + 1, bi);
             limb::row_acc<N>(E, a, bi);
-            asm("addc.u32 %0, %0, 0;" : "+r"(O[N - 1]));
+            asm volatile("addc.u32 %0, %0, 0;" : "+r"(O[N - 1]));
         }
         uint32_t m = E[0] * P::INV;
         limb::row_acc<N>(O, mod + 1, m);
         // O never carries out of N limbs (T < 2^(32(N+1))); this keeps the flag dead
-        asm("addc.u32 %0, %0, 0;" : "+r"(O[N - 1]));
+        asm volatile("addc.u32 %0, %0, 0;" : "+r"(O[N - 1]));
         limb::row_acc<N>(E, mod, m);
-        asm("addc.u32 %0, %0, 0;" : "+r"(O[N - 1]));
+        asm volatile("addc.u32 %0, %0, 0;" : "+r"(O[N - 1]));
     }
 
     // fp.tcc:50-228: a*b*R^-1 mod p, canonical.  Wide fields call one shared copy of the
@@ -213,11 +213,11 @@ struct Fp {
             mont_row(O, E, a.v, b.v[i + 1], false);
         }
         Fp t;
-        asm("add.cc.u32 %0, %1, %2;" : "=r"(t.v[0]) : "r"(E[0]), "r"(O[1]));
+        asm volatile("add.cc.u32 %0, %1, %2;" : "=r"(t.v[0]) : "r"(E[0]), "r"(O[1]));
 #pragma unroll
         for (int i = 1; i < N - 1; i++)
-            asm("addc.cc.u32 %0, %1, %2;" : "=r"(t.v[i]) : "r"(E[i]), "r"(O[i + 1]));
-        asm("addc.u32 %0, %1, 0;" : "=r"(t.v[N - 1]) : "r"(E[N - 1]));
+            asm volatile("addc.cc.u32 %0, %1, %2;" : "=r"(t.v[i]) : "r"(E[i]), "r"(O[i + 1]));
+        asm volatile("addc.u32 %0, %1, 0;" : "=r"(t.v[N - 1]) : "r"(E[N - 1]));
         return reduce_once(t);
     }
     B200_DEV static Fp sqr(const Fp &a) { return mul(a, a); }

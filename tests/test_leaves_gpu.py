@@ -1,0 +1,89 @@
+"""GPU parity of the leaves of the path against the unmodified reference (SURVEY.md §8a rows
+a7-a13): Montgomery field arithmetic (fp.tcc:50-727, fp2.tcc:79-168), as_bigint, and the group law
+incl. its exceptional cases (test_groups.cpp:25-116 is the model: 0+0, 0+P, P+0, P+Q, P+P, P-P)."""
+import numpy as np
+import pytest
+
+from oracle import pymodel as pm
+
+pytestmark = pytest.mark.gpu
+GROUPS = [0, 1, 2, 3]
+
+
+def rand_field(ref, fid, n, seed):
+    """n canonical Montgomery elements of field fid (any limbs < p are valid elements)."""
+    words = ref.lib().ref_field_bytes(fid) // 8
+    rng = np.random.default_rng(seed)
+    a = rng.integers(0, 1 << 63, size=(n, words), dtype=np.uint64) * np.uint64(2) + \
+        rng.integers(0, 2, size=(n, words), dtype=np.uint64)
+    # reduce through the reference itself: x -> x * 1 keeps it canonical (mul_reduce output < p)
+    a[:, -1] &= np.uint64(0x00FFFFFFFFFFFFFF)
+    if fid == ref.F_ALT_BN128_FQ2:
+        a[:, words // 2 - 1] &= np.uint64(0x00FFFFFFFFFFFFFF)
+    one = ref.field_op(fid, ref.OP_FROM_PLAIN, np.tile(np.eye(1, words, 0, dtype=np.uint64), (n, 1))) \
+        if fid != ref.F_ALT_BN128_FQ2 else None
+    return ref.field_op(fid, ref.OP_MUL, a, one) if one is not None else ref.field_op(fid, ref.OP_ADD, ref.field_op(fid, ref.OP_SQR, a), a)
+
+
+@pytest.mark.parametrize("gid", GROUPS)
+def test_coordinate_field_ops(engine, ref, gid):
+    fid = ref.FQ_OF_GROUP[gid]
+    n = 257
+    a = rand_field(ref, fid, n, 1)
+    b = rand_field(ref, fid, n, 2)
+    a[0] = 0
+    b[1] = 0
+    b[2] = a[2]
+    for eop, rop in [(engine.FQ_ADD, ref.OP_ADD), (engine.FQ_SUB, ref.OP_SUB),
+                     (engine.FQ_MUL, ref.OP_MUL)]:
+        np.testing.assert_array_equal(engine.debug_op(gid, eop, a, b), ref.field_op(fid, rop, a, b),
+                                      err_msg=f"op {eop}")
+    for eop, rop in [(engine.FQ_SQR, ref.OP_SQR), (engine.FQ_NEG, ref.OP_NEG)]:
+        np.testing.assert_array_equal(engine.debug_op(gid, eop, a), ref.field_op(fid, rop, a),
+                                      err_msg=f"op {eop}")
+    nz = a[3:40]
+    np.testing.assert_array_equal(engine.debug_op(gid, engine.FQ_INV, nz),
+                                  ref.field_op(fid, ref.OP_INV, nz))
+
+
+@pytest.mark.parametrize("gid", GROUPS)
+def test_scalar_field_as_bigint(engine, ref, gid):
+    g = pm.GROUPS[gid]
+    fid = ref.FR_OF_GROUP[gid]
+    vals = [0, 1, 2, g.fr.p - 1, g.fr.p - 2, 1 << 64, (1 << 200) + 12345] + \
+        [pm.sha512_rng(g.fr, i) for i in range(50)]
+    s = g.encode_scalars(vals)
+    got = engine.debug_op(gid, engine.FR_FROM_MONT, s)
+    np.testing.assert_array_equal(got, ref.field_op(fid, ref.OP_TO_PLAIN, s))
+    n64 = g.fr.limbs64
+    for row, v in zip(got, vals):
+        assert sum(int(row[j]) << (64 * j) for j in range(n64)) == v % g.fr.p
+    np.testing.assert_array_equal(engine.debug_op(gid, engine.FR_MUL, s, s[::-1].copy()),
+                                  ref.field_op(fid, ref.OP_MUL, s, s[::-1].copy()))
+
+
+@pytest.mark.parametrize("gid", GROUPS)
+def test_group_law(engine, ref, gid):
+    n = 64
+    aff = ref.gen_bases_walk(gid, n + 1)
+    P = ref.group_op(gid, ref.G_ADD, aff[:-1], aff[1:])   # non-normalised
+    Q = ref.group_op(gid, ref.G_DBL, aff[1:])
+    zero, _ = ref.group_constants(gid)
+    # exceptional rows: 0+0, 0+Q, P+0, P+P (different representatives), P+(-P)
+    P[0], Q[0] = zero, zero
+    P[1] = zero
+    negP = ref.group_op(gid, ref.G_NEG, P)
+    Q[2] = zero
+    Q[3] = ref.batch_to_special(gid, P[3:4])[0]
+    Q[4] = negP[4]
+    Q[5] = ref.batch_to_special(gid, negP[5:6])[0]
+
+    def same(got, want):
+        assert ref.group_eq(gid, got, want).all()
+        np.testing.assert_array_equal(ref.batch_to_special(gid, got), ref.batch_to_special(gid, want))
+
+    same(engine.debug_op(gid, engine.G_ADD, P, Q), ref.group_op(gid, ref.G_ADD, P, Q))
+    same(engine.debug_op(gid, engine.G_DBL, P), ref.group_op(gid, ref.G_DBL, P))
+    same(engine.debug_op(gid, engine.G_NEG, P), negP)
+    Qs = ref.batch_to_special(gid, Q)
+    same(engine.debug_op(gid, engine.G_MADD, P, Qs), ref.group_op(gid, ref.G_MIXED_ADD, P, Qs))
