@@ -46,6 +46,7 @@ enum Slot {
     SL_HIST,
     SL_OFFSETS,
     SL_CURSOR,
+    SL_TILE_SUMS,
     SL_SORTED,
     SL_BUCKETS,
     SL_CARRY_KEY_A,

@@ -17,9 +17,10 @@ namespace b200msm {
 
 inline unsigned cdiv(size_t a, size_t b) { return (unsigned)((a + b - 1) / b); }
 
-// Window size: minimises  n*W*10 + W*2^(c-1)*32  field multiplications (bucket accumulation with
-// 8M+2S mixed additions, bucket reduction with two 12M+2S additions per bucket plus the chunk
-// offset), W = ceil((bits + 1) / c).  The reference's own choice is pippenger_optimal_c
+// Window size: minimises  n*W*10 + W*2^(c-1)*53, W = ceil((bits + 1) / c): 10 field
+// multiplications per accumulated entry (8M+2S mixed addition) against the measured cost of one
+// bucket in the reduction (two 12M+2S additions + chunk offset, at lower occupancy; B200,
+// alt_bn128 G1, 2^24 points: 0.157 ns per entry vs 0.84 ns per bucket).  The reference's own choice is pippenger_optimal_c
 // (multiexp.tcc:35-40); any c gives the same group element.
 template <class C>
 uint32_t pick_window_bits(const Ctx &ctx, size_t n) {
@@ -29,7 +30,7 @@ uint32_t pick_window_bits(const Ctx &ctx, size_t n) {
     uint32_t best_c = 2;
     for (uint32_t c = 2; c <= 22; c++) {
         double W = (double)((bits + 1 + c - 1) / c);
-        double cost = (double)n * W * 10.0 + W * (double)(1u << (c - 1)) * 32.0;
+        double cost = (double)n * W * 10.0 + W * (double)(1u << (c - 1)) * 53.0;
         if (c == 2 || cost < best) best = cost, best_c = c;
     }
     return best_c;
@@ -126,8 +127,17 @@ bool sum_impl(Ctx &ctx, const void *d_raw, size_t count, void *d_out) {
 }
 
 // ------------------------------------------------------------------------------------------
-constexpr int SEG_FIRST = 32;   // sorted entries per thread, first accumulation round
-constexpr int SEG_CARRY = 16;   // carries per thread, later rounds
+constexpr int SEG_CARRY = 16;   // carries per thread, later accumulation rounds
+
+// Sorted entries per thread in the first accumulation round: long segments amortise the carry
+// rounds (one full addition per segment), short ones keep all SMs busy on small inputs.
+inline uint32_t pick_segment(const Ctx &ctx, size_t total) {
+    if (ctx.opt_segment > 0) return (uint32_t)ctx.opt_segment;
+    const size_t want_threads = 148 * 384 * 4;
+    uint32_t seg = 64;
+    while (seg > 8 && total / seg < want_threads) seg >>= 1;
+    return seg;
+}
 
 template <class C>
 bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_scalars, size_t n,
@@ -170,7 +180,14 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
     B200_LAUNCH_CHECK(ctx);
     B200_CUDA(cudaEventRecord(ctx.ev[PH_DIGITS + 1], st));
     // --- offsets
-    k_scan<<<1, 1024, 0, st>>>(hist, offsets, cursor, (uint32_t)M);
+    const uint32_t tiles = cdiv(M, SCAN_TILE);
+    uint32_t *tile_sums;
+    if (!reserve_as(ctx, SL_TILE_SUMS, ((size_t)tiles + 1) * 4, &tile_sums)) return false;
+    k_scan_tiles<<<tiles, SCAN_THREADS, 0, st>>>(hist, tile_sums, (uint32_t)M);
+    B200_LAUNCH_CHECK(ctx);
+    k_scan_tile_sums<<<1, 1024, 0, st>>>(tile_sums, tiles);
+    B200_LAUNCH_CHECK(ctx);
+    k_scan_apply<<<tiles, SCAN_THREADS, 0, st>>>(hist, tile_sums, tiles, offsets, cursor, (uint32_t)M);
     B200_LAUNCH_CHECK(ctx);
     B200_CUDA(cudaEventRecord(ctx.ev[PH_SCAN + 1], st));
     // --- scatter
@@ -184,22 +201,23 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
 
     // --- accumulation rounds
     if (total > 0) {
-        size_t t1 = ((size_t)total + SEG_FIRST - 1) / SEG_FIRST;
+        const uint32_t seg = pick_segment(ctx, total);
+        size_t t1 = ((size_t)total + seg - 1) / seg;
         size_t t2 = (t1 + SEG_CARRY - 1) / SEG_CARRY;
         uint32_t *keyA, *ptA, *keyB, *ptB;
         if (!reserve_as(ctx, SL_CARRY_KEY_A, t1 * 4, &keyA)) return false;
         if (!reserve_as(ctx, SL_CARRY_PT_A, t1 * R::XW * 4, &ptA)) return false;
         if (!reserve_as(ctx, SL_CARRY_KEY_B, t2 * 4, &keyB)) return false;
         if (!reserve_as(ctx, SL_CARRY_PT_B, t2 * R::XW * 4, &ptB)) return false;
-        k_accum_first<C, SEG_FIRST><<<cdiv(t1, 128), 128, 0, st>>>(
-            sorted, total, (const uint32_t *)d_aff, buckets, keyA, ptA);
+        k_accum_first<C><<<cdiv(t1, 128), 128, 0, st>>>(sorted, total, seg, (const uint32_t *)d_aff,
+                                                        buckets, keyA, ptA);
         B200_LAUNCH_CHECK(ctx);
         B200_CUDA(cudaEventRecord(ctx.ev[PH_ACCUM + 1], st));
         size_t len = t1;
         while (true) {
             size_t tn = (len + SEG_CARRY - 1) / SEG_CARRY;
-            k_accum_carry<C, SEG_CARRY><<<cdiv(tn, 128), 128, 0, st>>>(keyA, ptA, (uint32_t)len,
-                                                                       buckets, keyB, ptB);
+            k_accum_carry<C><<<cdiv(tn, 128), 128, 0, st>>>(keyA, ptA, (uint32_t)len, SEG_CARRY,
+                                                            buckets, keyB, ptB);
             B200_LAUNCH_CHECK(ctx);
             if (tn == 1) break;  // a single thread owns every run it sees: no carries remain
             std::swap(keyA, keyB);
@@ -221,7 +239,7 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
     k_bucket_reduce<C><<<dim3(cdiv(nchunks, 64), W), 64, 0, st>>>(buckets, hist, B, K, chunks);
     B200_LAUNCH_CHECK(ctx);
     B200_CUDA(cudaEventRecord(ctx.ev[PH_BUCKET_REDUCE + 1], st));
-    constexpr int WR_THREADS = 64;
+    constexpr int WR_THREADS = 128;
     const size_t wr_smem = (size_t)WR_THREADS * R::XW * 4;
     static bool attr_set = false;
     if (!attr_set) {

@@ -4,7 +4,7 @@
 // Pipeline (one launch each, all windows at once):
 //   k_digits        scalars: Montgomery -> plain (fp.tcc:270-281) -> signed c-bit digits
 //                   (field_utils.tcc:167-239 restated as a single carry pass) + bucket histogram
-//   k_scan          exclusive prefix sum of the histogram -> bucket offsets
+//   k_scan_*        exclusive prefix sum of the histogram -> bucket offsets (3 launches)
 //   k_scatter       counting-sort scatter of (bucket, point index | sign) pairs
 //   k_accum_first   balanced segmented accumulation: every thread sums SEG consecutive sorted
 //                   entries with mixed additions (multiexp.tcc:319-345 / :45-81); sums of buckets
@@ -68,30 +68,91 @@ __global__ void k_digits(const uint32_t *__restrict__ scalars, const uint8_t *__
 }
 
 // ------------------------------------------------------------------------------------------
-// exclusive scan of m counters (single block); offsets has m + 1 entries, cursor m
-static __global__ void k_scan(const uint32_t *__restrict__ hist, uint32_t *__restrict__ offsets,
-                       uint32_t *__restrict__ cursor, uint32_t m) {
-    __shared__ uint32_t part[1024];
-    const uint32_t t = threadIdx.x, nt = blockDim.x;
-    const uint32_t per = (m + nt - 1) / nt;
-    const uint32_t lo = min(m, t * per), hi = min(m, lo + per);
-    uint32_t s = 0;
-    for (uint32_t k = lo; k < hi; k++) s += hist[k];
-    part[t] = s;
+// Exclusive scan of the m bucket counters in three launches: per-tile sums, scan of the tile
+// sums (one block), per-tile scan + tile offset.  offsets has m + 1 entries, cursor m.
+constexpr int SCAN_THREADS = 256;
+constexpr int SCAN_ITEMS = 8;                          // counters per thread
+constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;   // counters per block
+
+__device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t *warp_sums,
+                                                         uint32_t &block_total) {
+    const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    uint32_t inc = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= d) inc += o;
+    }
+    if (lane == 31) warp_sums[wid] = inc;
     __syncthreads();
-    for (uint32_t d = 1; d < nt; d <<= 1) {
-        uint32_t v = t >= d ? part[t - d] : 0;
-        __syncthreads();
-        part[t] += v;
+    if (wid == 0) {
+        uint32_t w = lane < (blockDim.x >> 5) ? warp_sums[lane] : 0;
+        uint32_t winc = w;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            uint32_t o = __shfl_up_sync(0xffffffffu, winc, d);
+            if (lane >= d) winc += o;
+        }
+        warp_sums[lane] = winc - w;                    // exclusive prefix of warp totals
+        if (lane == 31) warp_sums[32] = winc;          // block total
+    }
+    __syncthreads();
+    block_total = warp_sums[32];
+    return warp_sums[wid] + inc - v;
+}
+
+static __global__ void __launch_bounds__(SCAN_THREADS)
+    k_scan_tiles(const uint32_t *__restrict__ hist, uint32_t *__restrict__ tile_sums, uint32_t m) {
+    __shared__ uint32_t ws[33];
+    const uint32_t base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
+    uint32_t s = 0;
+#pragma unroll
+    for (int j = 0; j < SCAN_ITEMS; j++)
+        if (base + j < m) s += hist[base + j];
+    uint32_t total;
+    block_exclusive_scan(s, ws, total);
+    if (threadIdx.x == 0) tile_sums[blockIdx.x] = total;
+}
+
+// in-place exclusive scan of the tile sums by one block; tile_sums[tiles] = grand total
+static __global__ void __launch_bounds__(1024)
+    k_scan_tile_sums(uint32_t *__restrict__ tile_sums, uint32_t tiles) {
+    __shared__ uint32_t ws[33];
+    uint32_t carry = 0;
+    for (uint32_t lo = 0; lo < tiles; lo += 1024) {
+        const uint32_t k = lo + threadIdx.x;
+        uint32_t v = k < tiles ? tile_sums[k] : 0, total;
+        uint32_t ex = block_exclusive_scan(v, ws, total);
+        if (k < tiles) tile_sums[k] = carry + ex;
+        carry += total;
         __syncthreads();
     }
-    uint32_t run = part[t] - s;
-    for (uint32_t k = lo; k < hi; k++) {
-        offsets[k] = run;
-        cursor[k] = run;
-        run += hist[k];
+    if (threadIdx.x == 0) tile_sums[tiles] = carry;
+}
+
+static __global__ void __launch_bounds__(SCAN_THREADS)
+    k_scan_apply(const uint32_t *__restrict__ hist, const uint32_t *__restrict__ tile_sums,
+                 uint32_t tiles, uint32_t *__restrict__ offsets, uint32_t *__restrict__ cursor,
+                 uint32_t m) {
+    __shared__ uint32_t ws[33];
+    const uint32_t base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
+    uint32_t v[SCAN_ITEMS], s = 0;
+#pragma unroll
+    for (int j = 0; j < SCAN_ITEMS; j++) {
+        v[j] = base + j < m ? hist[base + j] : 0;
+        s += v[j];
     }
-    if (t == nt - 1) offsets[m] = part[t];
+    uint32_t total;
+    uint32_t run = tile_sums[blockIdx.x] + block_exclusive_scan(s, ws, total);
+#pragma unroll
+    for (int j = 0; j < SCAN_ITEMS; j++) {
+        if (base + j < m) {
+            offsets[base + j] = run;
+            cursor[base + j] = run;
+        }
+        run += v[j];
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) offsets[m] = tile_sums[tiles];
 }
 
 // ------------------------------------------------------------------------------------------
@@ -109,10 +170,10 @@ __global__ void k_scatter(const int32_t *__restrict__ digits, uint32_t *__restri
 }
 
 // ------------------------------------------------------------------------------------------
-// First accumulation round: thread t owns sorted[t*SEG, (t+1)*SEG).
-template <class C, int SEG>
+// First accumulation round: thread t owns sorted[t*SEG, (t+1)*SEG) (SEG chosen by the host).
+template <class C>
 __global__ void __launch_bounds__(128)
-    k_accum_first(const Entry *__restrict__ sorted, uint32_t total,
+    k_accum_first(const Entry *__restrict__ sorted, uint32_t total, uint32_t SEG,
                   const uint32_t *__restrict__ aff, uint32_t *__restrict__ bucket_acc,
                   uint32_t *__restrict__ carry_key, uint32_t *__restrict__ carry_pt) {
     using R = Raw<C>;
@@ -162,10 +223,10 @@ __global__ void __launch_bounds__(128)
 
 // Later rounds: the carry list (keys ascending, one XYZZ point each) is reduced the same way with
 // full additions; sums of runs that begin a bucket in this list are added into bucket_acc.
-template <class C, int SEG>
+template <class C>
 __global__ void __launch_bounds__(128)
     k_accum_carry(const uint32_t *__restrict__ keys, const uint32_t *__restrict__ pts,
-                  uint32_t total, uint32_t *__restrict__ bucket_acc,
+                  uint32_t total, uint32_t SEG, uint32_t *__restrict__ bucket_acc,
                   uint32_t *__restrict__ carry_key, uint32_t *__restrict__ carry_pt) {
     using R = Raw<C>;
     using F = typename C::Fq;
