@@ -169,6 +169,7 @@ def main():
     import torch.distributed as dist
 
     import libff_b200 as m
+    from libff_b200 import distributed as D
     from libff_b200 import synthetic as syn
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the MSM engine has no CPU path")
@@ -199,7 +200,6 @@ def main():
         raise SystemExit("bench.py: MSM result does not match the closed form; not timing")
 
     rb, rs = m.ResidentBases(gid, bases), m.ResidentScalars(gid, scalars)
-    gather = torch.zeros(world * gb // 8, dtype=torch.int64, device="cuda") if world > 1 else None
 
     def barrier():
         if world > 1:
@@ -210,10 +210,8 @@ def main():
         """gather the per-GPU partial points and add them (multiexp.tcc:681-685)"""
         if world == 1:
             return partial
-        mine = torch.from_numpy(partial.view(np.int64)).cuda()
-        dist.all_gather_into_tensor(gather, mine)
-        allp = gather.cpu().numpy().view(np.uint64).reshape(world, gb // 8)
-        return m.group_sum(gid, allp) if rank == 0 else partial
+        allp = D.gather_partials(partial)  # NCCL all_gather of sizeof(G) bytes per rank
+        return D.combine_partials(gid, allp) if rank == 0 else partial
 
     def step_resident():
         return combine(m.multi_exp_resident(rb, rs))

@@ -1,0 +1,274 @@
+/** libff_b200.hpp -- source-level drop-in that routes libff's MSM hot path to the B200 engine.
+ *
+ * Include this header immediately after
+ *     #include <libff/algebra/scalar_multiplication/multiexp.hpp>
+ * (and the curve headers) and before any call site, then link libb200msm.so.  It provides explicit
+ * (full) specialisations of the reference templates for the four groups of the path:
+ *
+ *   libff::multi_exp<G, Fr, multi_exp_method_BDLO12 | _BDLO12_signed, normal | special>
+ *                                                   multiexp.hpp:63-73, multiexp.tcc:643-688
+ *   libff::internal::multi_exp_implementation<G, Fr, Method, Form>::multi_exp_inner
+ *                                                   multiexp.tcc:198-212, 276-381, 507-633
+ *   libff::batch_exp<G, Fr>(scalar_size, window, table, v[, num_entries])
+ *                                                   multiexp.hpp:120-134, multiexp.tcc:875-915
+ *   libff::batch_to_special<G>(vec)                 multiexp.hpp:144, multiexp.tcc:949-974
+ *
+ * for G in { alt_bn128_G1, alt_bn128_G2, bls12_377_G1, bw6_761_G1 } with their scalar fields.
+ * Call sites stay source-identical (libff's own test, test_multiexp.cpp, compiles unchanged: see
+ * tests/cpp/dropin_test.cpp).  Everything forwards to the C ABI of include/b200msm.h with
+ * `&*vec.begin()`: no conversion, libff's in-memory layout is the wire format.
+ *
+ * Semantics kept from the reference: the result is the same group element (operator== true,
+ * identical affine coordinates); batch_to_special output is limb-identical; n == 0 returns
+ * G::zero().  Differences, all permitted by the reference's contract: the returned (X:Y:Z)
+ * representative may differ; `chunks` (an OpenMP split hint, multiexp.tcc:655-687) is ignored;
+ * the profiling printf side effects of batch_exp / batch_to_special (multiexp.tcc:887-913, 951,
+ * 973) are dropped.  There is no CPU fallback: if the engine cannot run (no CUDA device, library
+ * error) a std::runtime_error carrying b200msm_last_error() is thrown.
+ *
+ * The process binds to one CUDA device on first use: libff::b200::init(device) or, lazily,
+ * $B200MSM_DEVICE / $LOCAL_RANK / 0.
+ */
+#ifndef LIBFF_B200_HPP_
+#define LIBFF_B200_HPP_
+
+#include <cstdlib>
+#include <libff/algebra/curves/alt_bn128/alt_bn128_pp.hpp>
+#include <libff/algebra/curves/bls12_377/bls12_377_pp.hpp>
+#include <libff/algebra/curves/bw6_761/bw6_761_pp.hpp>
+#include <libff/algebra/scalar_multiplication/multiexp.hpp>
+#include <mutex>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "b200msm.h"
+
+namespace libff
+{
+namespace b200
+{
+
+template<typename GroupT> struct group_id;
+template<> struct group_id<alt_bn128_G1> {
+    static constexpr uint32_t value = B200MSM_ALT_BN128_G1;
+};
+template<> struct group_id<alt_bn128_G2> {
+    static constexpr uint32_t value = B200MSM_ALT_BN128_G2;
+};
+template<> struct group_id<bls12_377_G1> {
+    static constexpr uint32_t value = B200MSM_BLS12_377_G1;
+};
+template<> struct group_id<bw6_761_G1> {
+    static constexpr uint32_t value = B200MSM_BW6_761_G1;
+};
+
+[[noreturn]] inline void fail(const char *what)
+{
+    throw std::runtime_error(
+        std::string(what) + ": " + b200msm_last_error() + " (b200msm has no CPU fallback)");
+}
+
+/// Binds the process to a CUDA device (b200msm_init). Safe to call repeatedly.
+inline void init(int device)
+{
+    if (!b200msm_init(device)) {
+        fail("b200msm_init");
+    }
+}
+
+inline void ensure_init()
+{
+    static std::once_flag once;
+    std::call_once(once, [] {
+        const char *d = std::getenv("B200MSM_DEVICE");
+        if (!d) {
+            d = std::getenv("LOCAL_RANK");
+        }
+        init(d ? std::atoi(d) : 0);
+    });
+}
+
+/// The layout contract of include/b200msm.h, checked at compile time against libff's types.
+template<typename GroupT, typename FieldT> struct layout_check {
+    static_assert(
+        sizeof(FieldT) == FieldT::num_limbs * sizeof(mp_limb_t),
+        "scalar must be exactly its Montgomery limbs");
+    static_assert(sizeof(mp_limb_t) == 8, "64-bit limbs expected");
+};
+
+template<typename GroupT, typename FieldT>
+GroupT multi_exp(
+    typename std::vector<GroupT>::const_iterator vec_start,
+    typename std::vector<GroupT>::const_iterator vec_end,
+    typename std::vector<FieldT>::const_iterator scalar_start,
+    typename std::vector<FieldT>::const_iterator scalar_end,
+    multi_exp_base_form form)
+{
+    (void)sizeof(layout_check<GroupT, FieldT>);
+    const size_t n = vec_end - vec_start;
+    if ((size_t)(scalar_end - scalar_start) != n) {
+        throw std::runtime_error("b200 multi_exp: bases and scalars differ in length");
+    }
+    if (n == 0) {
+        // multiexp.tcc:291-309; &*vec_start would not be dereferenceable
+        return GroupT::zero();
+    }
+    ensure_init();
+    if (sizeof(GroupT) != b200msm_group_bytes(group_id<GroupT>::value) ||
+        sizeof(FieldT) != b200msm_scalar_bytes(group_id<GroupT>::value)) {
+        throw std::runtime_error("b200 multi_exp: sizeof(GroupT)/sizeof(FieldT) mismatch");
+    }
+    GroupT result;
+    const bool ok = b200msm_multi_exp(
+        group_id<GroupT>::value,
+        (const void *)&*vec_start,
+        n * sizeof(GroupT),
+        (const void *)&*scalar_start,
+        n * sizeof(FieldT),
+        n,
+        form == multi_exp_base_form_special ? B200MSM_FORM_SPECIAL : B200MSM_FORM_NORMAL,
+        (void *)&result,
+        sizeof(GroupT));
+    if (!ok) {
+        fail("b200msm_multi_exp");
+    }
+    return result;
+}
+
+template<typename GroupT, typename FieldT>
+std::vector<GroupT> batch_exp(
+    const size_t scalar_size,
+    const size_t window,
+    const window_table<GroupT> &table,
+    const std::vector<FieldT> &v,
+    size_t num_entries)
+{
+    std::vector<GroupT> res(num_entries, table[0][0]); // multiexp.tcc:890
+    if (num_entries == 0) {
+        return res;
+    }
+    if (num_entries > v.size()) {
+        throw std::runtime_error("b200 batch_exp: num_entries exceeds the scalar vector");
+    }
+    ensure_init();
+    std::vector<const void *> rows(table.size());
+    for (size_t r = 0; r < table.size(); ++r) {
+        if (table[r].size() != table[0].size()) {
+            // get_window_table gives every row 1 << window entries (multiexp.tcc:828-836)
+            throw std::runtime_error("b200 batch_exp: ragged window table");
+        }
+        rows[r] = (const void *)table[r].data();
+    }
+    const bool ok = b200msm_batch_exp(
+        group_id<GroupT>::value,
+        scalar_size,
+        window,
+        rows.data(),
+        rows.size(),
+        table[0].size(),
+        (const void *)v.data(),
+        num_entries * sizeof(FieldT),
+        num_entries,
+        (void *)res.data(),
+        num_entries * sizeof(GroupT));
+    if (!ok) {
+        fail("b200msm_batch_exp");
+    }
+    return res;
+}
+
+template<typename GroupT> void batch_to_special(std::vector<GroupT> &vec)
+{
+    if (vec.empty()) {
+        return;
+    }
+    ensure_init();
+    if (!b200msm_batch_to_special(
+            group_id<GroupT>::value,
+            (void *)vec.data(),
+            vec.size() * sizeof(GroupT),
+            vec.size())) {
+        fail("b200msm_batch_to_special");
+    }
+}
+
+} // namespace b200
+} // namespace libff
+
+// ---- explicit specialisations of the reference templates ------------------------------------
+
+#define LIBFF_B200_SPECIALISE_MULTI_EXP(G, F, METHOD, FORM)                                   \
+    namespace libff                                                                           \
+    {                                                                                         \
+    template<>                                                                                \
+    inline G multi_exp<G, F, METHOD, FORM>(                                                   \
+        std::vector<G>::const_iterator vec_start,                                             \
+        std::vector<G>::const_iterator vec_end,                                               \
+        std::vector<F>::const_iterator scalar_start,                                          \
+        std::vector<F>::const_iterator scalar_end,                                            \
+        const size_t chunks)                                                                  \
+    {                                                                                         \
+        (void)chunks; /* OpenMP split hint of the CPU path, multiexp.tcc:655-687 */           \
+        return b200::multi_exp<G, F>(vec_start, vec_end, scalar_start, scalar_end, FORM);     \
+    }                                                                                         \
+    namespace internal                                                                        \
+    {                                                                                         \
+    template<> class multi_exp_implementation<G, F, METHOD, FORM>                             \
+    {                                                                                         \
+    public:                                                                                   \
+        static G multi_exp_inner(                                                             \
+            std::vector<G>::const_iterator bases,                                             \
+            std::vector<G>::const_iterator bases_end,                                         \
+            std::vector<F>::const_iterator exponents,                                         \
+            std::vector<F>::const_iterator exponents_end)                                     \
+        {                                                                                     \
+            return b200::multi_exp<G, F>(bases, bases_end, exponents, exponents_end, FORM);   \
+        }                                                                                     \
+    };                                                                                        \
+    }                                                                                         \
+    }
+
+#define LIBFF_B200_SPECIALISE_GROUP(G, F)                                                     \
+    LIBFF_B200_SPECIALISE_MULTI_EXP(G, F, multi_exp_method_BDLO12, multi_exp_base_form_normal) \
+    LIBFF_B200_SPECIALISE_MULTI_EXP(G, F, multi_exp_method_BDLO12, multi_exp_base_form_special) \
+    LIBFF_B200_SPECIALISE_MULTI_EXP(                                                          \
+        G, F, multi_exp_method_BDLO12_signed, multi_exp_base_form_normal)                     \
+    LIBFF_B200_SPECIALISE_MULTI_EXP(                                                          \
+        G, F, multi_exp_method_BDLO12_signed, multi_exp_base_form_special)                    \
+    namespace libff                                                                           \
+    {                                                                                         \
+    template<>                                                                                \
+    inline std::vector<G> batch_exp<G, F>(                                                    \
+        const size_t scalar_size,                                                             \
+        const size_t window,                                                                  \
+        const window_table<G> &table,                                                         \
+        const std::vector<F> &v,                                                              \
+        size_t num_entries)                                                                   \
+    {                                                                                         \
+        return b200::batch_exp<G, F>(scalar_size, window, table, v, num_entries);             \
+    }                                                                                         \
+    template<>                                                                                \
+    inline std::vector<G> batch_exp<G, F>(                                                    \
+        const size_t scalar_size,                                                             \
+        const size_t window,                                                                  \
+        const window_table<G> &table,                                                         \
+        const std::vector<F> &v)                                                              \
+    {                                                                                         \
+        return b200::batch_exp<G, F>(scalar_size, window, table, v, v.size());                \
+    }                                                                                         \
+    template<> inline void batch_to_special<G>(std::vector<G> & vec)                          \
+    {                                                                                         \
+        b200::batch_to_special<G>(vec);                                                       \
+    }                                                                                         \
+    }
+
+LIBFF_B200_SPECIALISE_GROUP(alt_bn128_G1, alt_bn128_Fr)
+LIBFF_B200_SPECIALISE_GROUP(alt_bn128_G2, alt_bn128_Fr)
+LIBFF_B200_SPECIALISE_GROUP(bls12_377_G1, bls12_377_Fr)
+LIBFF_B200_SPECIALISE_GROUP(bw6_761_G1, bw6_761_Fr)
+
+#undef LIBFF_B200_SPECIALISE_GROUP
+#undef LIBFF_B200_SPECIALISE_MULTI_EXP
+
+#endif // LIBFF_B200_HPP_

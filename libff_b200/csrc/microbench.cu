@@ -2,6 +2,7 @@
 // integer peak, so the denominators used by bench.py are measured here.
 //   imad32     independent 32-bit IMAD chains (mad.lo.u32)
 //   imadwide   independent IMAD.WIDE.U32 chains (mad.wide.u32, 64-bit accumulate)
+//   dfma       independent FP64 FMA chains; dfma_plus_imad: the two interleaved 1:1
 //   mont<N>    back-to-back Montgomery products of the field code itself (fp.cuh)
 // Prints one JSON object.  Usage: microbench [iters]
 #include <cuda_runtime.h>
@@ -61,6 +62,44 @@ __global__ void k_imadwide(uint64_t *out, uint32_t seed, int iters) {
     out[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
 
+// FP64 pipe: independent DFMA chains; and DFMA interleaved 1:1 with IMAD (do the two pipes overlap?)
+__global__ void k_dfma(double *out, double seed, int iters) {
+    double a[ILP], m = seed, x = 1e-9 * threadIdx.x;
+#pragma unroll
+    for (int i = 0; i < ILP; i++) a[i] = seed + i + threadIdx.x;
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int u = 0; u < 8; u++)
+#pragma unroll
+            for (int i = 0; i < ILP; i++)
+                asm volatile("fma.rn.f64 %0, %0, %1, %2;" : "+d"(a[i]) : "d"(m), "d"(x));
+    }
+    double s = 0;
+#pragma unroll
+    for (int i = 0; i < ILP; i++) s += a[i];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+__global__ void k_dfma_imad(double *out, double seed, int iters) {
+    double a[ILP], m = seed, x = 1e-9 * threadIdx.x;
+    uint32_t b[ILP], mi = (uint32_t)seed | 1u, xi = threadIdx.x + 3;
+#pragma unroll
+    for (int i = 0; i < ILP; i++) a[i] = seed + i + threadIdx.x, b[i] = i + threadIdx.x;
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int u = 0; u < 8; u++)
+#pragma unroll
+            for (int i = 0; i < ILP; i++) {
+                asm volatile("fma.rn.f64 %0, %0, %1, %2;" : "+d"(a[i]) : "d"(m), "d"(x));
+                asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(b[i]) : "r"(mi), "r"(xi));
+            }
+    }
+    double s = 0;
+#pragma unroll
+    for (int i = 0; i < ILP; i++) s += a[i] + b[i];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
 template <class P>
 __global__ void k_mont(uint32_t *out, uint32_t seed, int iters) {
     using F = Fp<P>;
@@ -116,6 +155,10 @@ int main(int argc, char **argv) {
         printf(", \"imad32_w%d_Tops\": %.3f", warps, ops / ms * 1e-9);
         ms = time_ms([&] { k_imadwide<<<blocks, threads>>>((uint64_t *)out, 12345, iters); });
         printf(", \"imadwide_w%d_Tops\": %.3f", warps, ops / ms * 1e-9);
+        ms = time_ms([&] { k_dfma<<<blocks, threads>>>((double *)out, 1.0000001, iters); });
+        printf(", \"dfma_w%d_Tops\": %.3f", warps, ops / ms * 1e-9);
+        ms = time_ms([&] { k_dfma_imad<<<blocks, threads>>>((double *)out, 1.0000001, iters); });
+        printf(", \"dfma_plus_imad_w%d_Tpairs\": %.3f", warps, ops / ms * 1e-9);
     }
     for (int wps : {4, 8, 12, 16}) {  // resident warps per SM
         int blocks = sms * wps / 4;

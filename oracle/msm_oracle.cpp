@@ -1103,6 +1103,18 @@ long orc_signed_digit(int fid, const void *scalar_mont, size_t c, size_t idx) {
     FIELD_SWITCH(fid, return signed_digit_of<F>((const uint64_t *)scalar_mont, c, idx));
     return 0;
 }
+// field_get_digit (field_utils.tcc:50-100) of the plain value of a Montgomery-form scalar
+size_t orc_get_digit(int fid, const void *scalar_mont, size_t c, size_t idx) {
+    init_all();
+    FIELD_SWITCH(fid, {
+        F x;
+        x.load((const uint64_t *)scalar_mont);
+        Big<F::N> v;
+        x.as_bigint(v.d);
+        return get_digit(v, c, idx);
+    });
+    return 0;
+}
 size_t orc_num_signed_digits(int fid, size_t c) {
     init_all();
     FIELD_SWITCH(fid, return num_signed_digits<F>(c));

@@ -65,6 +65,7 @@ def lib():
             "orc_field_op": (None, [i32, i32, vp, vp, vp, sz]),
             "orc_signed_digit": (C.c_long, [i32, vp, sz, sz]),
             "orc_num_signed_digits": (sz, [i32, sz]),
+            "orc_get_digit": (sz, [i32, vp, sz, sz]),
             "orc_pippenger_optimal_c": (sz, [sz]),
         }
         for name, (res, args) in sigs.items():
@@ -188,6 +189,11 @@ def field_op(fid, op, a, b=None) -> np.ndarray:
 def signed_digit(fid, scalar_mont, c, idx) -> int:
     s = _c(scalar_mont)
     return int(lib().orc_signed_digit(fid, _p(s), c, idx))
+
+
+def get_digit(fid, scalar_mont, c, idx) -> int:
+    s = _c(scalar_mont)
+    return int(lib().orc_get_digit(fid, _p(s), c, idx))
 
 
 def num_signed_digits(fid, c) -> int:
