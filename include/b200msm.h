@@ -109,7 +109,9 @@ bool b200msm_debug_op(uint32_t group, uint32_t op, const void *a, const void *b,
                       size_t bytes, size_t n);
 
 /* Tuning and measurement (not part of the reference surface).
- * option: "window_bits" (0 = automatic), "segment" (entries per thread of the accumulation). */
+ * option: "window_bits" (0 = automatic), "segment" (entries per thread of the accumulation),
+ * "h2d_parts" (point ranges a host-buffer multi_exp is cut into so that uploads overlap the
+ * computation; 0 = automatic, 1 = no overlap). */
 bool b200msm_set_option(const char *name, int64_t value);
 /* CUDA-event timings (ms) of the phases of the most recent multi_exp on this thread's engine,
  * measured on the engine's own stream.  Writes up to `cap` values, returns how many phases exist.

@@ -3,9 +3,12 @@
 // buffers, outputs written only on success, no exceptions across the boundary.
 #include "../../include/b200msm.h"
 
+#include <atomic>
+#include <condition_variable>
 #include <cstring>
 #include <map>
 #include <mutex>
+#include <thread>
 
 #include "engine.hpp"
 
@@ -114,12 +117,8 @@ bool mark_all(Ctx &ctx, int from) {
     return true;
 }
 
-bool run_msm(Ctx &ctx, const GroupOps *ops, const void *d_aff, const uint8_t *d_inf,
-             const void *d_scalars, size_t n, void *out) {
-    void *d_out;
-    if (!ctx.reserve(SL_OUT, ops->group_bytes, &d_out)) return false;
-    if (!mark_all(ctx, PH_INGEST + 1)) return false;
-    if (!ops->msm(ctx, d_aff, d_inf, d_scalars, n, d_out)) return false;
+// D2H of the result + phase timings; the only host synchronisation point of a call
+bool finish_msm(Ctx &ctx, const GroupOps *ops, const void *d_out, void *out) {
     std::vector<unsigned char> tmp(ops->group_bytes);
     B200_CUDA(cudaMemcpyAsync(tmp.data(), d_out, ops->group_bytes, cudaMemcpyDeviceToHost, ctx.stream));
     if (!collect_timings(ctx)) return false;
@@ -127,6 +126,42 @@ bool run_msm(Ctx &ctx, const GroupOps *ops, const void *d_aff, const uint8_t *d_
     memcpy(out, tmp.data(), ops->group_bytes);
     return true;
 }
+
+bool run_msm(Ctx &ctx, const GroupOps *ops, const void *d_aff, const uint8_t *d_inf,
+             const void *d_scalars, size_t n, void *out) {
+    void *d_out;
+    if (!ctx.reserve(SL_OUT, ops->group_bytes, &d_out)) return false;
+    if (!mark_all(ctx, PH_INGEST + 1)) return false;
+    if (!ops->msm(ctx, d_aff, d_inf, d_scalars, n, d_out)) return false;
+    return finish_msm(ctx, ops, d_out, out);
+}
+
+// How many point ranges a host-buffer multi_exp is cut into so that the upload of range k + 1
+// overlaps the computation of range k (each range is an independent MSM; the partial results are
+// added at the end exactly like the reference's per-chunk partials, multiexp.tcc:681-685).
+size_t pick_parts(const Ctx &ctx, size_t n) {
+    if (ctx.opt_h2d_parts > 0) return std::min<size_t>((size_t)ctx.opt_h2d_parts, std::max<size_t>(n, 1));
+    if (n < ((size_t)1 << 21)) return 1;
+    if (n < ((size_t)1 << 23)) return 2;
+    return 3;
+}
+
+// Uploads the parts in order on the copy stream from a helper thread (a cudaMemcpyAsync from
+// pageable memory blocks its caller, which must not be the thread that launches the kernels).
+struct Uploader {
+    std::mutex m;
+    std::condition_variable cv;
+    int issued = 0;
+    bool failed = false;
+    std::thread th;
+    void wait_for(int k) {
+        std::unique_lock<std::mutex> lk(m);
+        cv.wait(lk, [&] { return issued > k || failed; });
+    }
+    ~Uploader() {
+        if (th.joinable()) th.join();
+    }
+};
 
 }  // namespace
 }  // namespace b200msm
@@ -152,7 +187,10 @@ bool b200msm_init(int device) {
     Ctx *ctx = new Ctx();
     ctx->device = device;
     B200_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    B200_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
     for (auto &e : ctx->ev) B200_CUDA(cudaEventCreate(&e));
+    for (auto &e : ctx->ev_copy) B200_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    B200_CUDA(cudaEventCreateWithFlags(&ctx->ev_sync, cudaEventDisableTiming));
     g_ctx = ctx;
     return true;
 }
@@ -169,6 +207,9 @@ void b200msm_shutdown(void) {
     g_resident.clear();
     g_ctx->release_all();
     for (auto &e : g_ctx->ev) cudaEventDestroy(e);
+    for (auto &e : g_ctx->ev_copy) cudaEventDestroy(e);
+    cudaEventDestroy(g_ctx->ev_sync);
+    cudaStreamDestroy(g_ctx->copy_stream);
     cudaStreamDestroy(g_ctx->stream);
     delete g_ctx;
     g_ctx = nullptr;
@@ -197,18 +238,69 @@ bool b200msm_multi_exp(uint32_t group, const void *bases, size_t bases_bytes, co
         return set_error("multi_exp: buffer sizes do not match n = %zu", n), false;
     if (!out || (n > 0 && (!bases || !scalars))) return set_error("multi_exp: null buffer"), false;
     Ctx &ctx = *g_ctx;
-    void *d_raw, *d_aff, *d_inf, *d_sc;
+    void *d_raw, *d_aff, *d_inf, *d_sc, *d_out, *d_parts;
     if (!ctx.reserve(SL_RAW, bases_bytes, &d_raw)) return false;
     if (!ctx.reserve(SL_AFF, n * ops->affine_bytes, &d_aff)) return false;
     if (!ctx.reserve(SL_INF, n, &d_inf)) return false;
     if (!ctx.reserve(SL_SCALARS, scalars_bytes, &d_sc)) return false;
+    if (!ctx.reserve(SL_OUT, ops->group_bytes, &d_out)) return false;
+    const size_t parts = pick_parts(ctx, n);
+    if (!ctx.reserve(SL_PARTIALS, parts * ops->group_bytes, &d_parts)) return false;
     B200_CUDA(cudaEventRecord(ctx.ev[0], ctx.stream));
-    if (n > 0) {
-        B200_CUDA(cudaMemcpyAsync(d_raw, bases, bases_bytes, cudaMemcpyHostToDevice, ctx.stream));
-        B200_CUDA(cudaMemcpyAsync(d_sc, scalars, scalars_bytes, cudaMemcpyHostToDevice, ctx.stream));
-        if (!ops->ingest(ctx, d_raw, n, base_form, d_aff, (uint8_t *)d_inf)) return false;
+    if (parts <= 1) {
+        if (n > 0) {
+            B200_CUDA(cudaMemcpyAsync(d_raw, bases, bases_bytes, cudaMemcpyHostToDevice, ctx.stream));
+            B200_CUDA(cudaMemcpyAsync(d_sc, scalars, scalars_bytes, cudaMemcpyHostToDevice, ctx.stream));
+            if (!ops->ingest(ctx, d_raw, n, base_form, d_aff, (uint8_t *)d_inf)) return false;
+        }
+        return run_msm(ctx, ops, d_aff, (const uint8_t *)d_inf, d_sc, n, out);
     }
-    return run_msm(ctx, ops, d_aff, (const uint8_t *)d_inf, d_sc, n, out);
+    // ---- pipelined: upload of range k + 1 (copy stream) under the MSM of range k
+    const size_t gb = ops->group_bytes, sb = ops->scalar_bytes, ab = ops->affine_bytes;
+    const size_t one = n / parts;
+    auto lo_of = [&](size_t k) { return k * one; };
+    auto hi_of = [&](size_t k) { return k + 1 == parts ? n : (k + 1) * one; };
+    // the compute stream must not overwrite the staging buffers of a previous call that is
+    // still in flight: the copy stream starts after everything queued so far
+    B200_CUDA(cudaEventRecord(ctx.ev_sync, ctx.stream));
+    B200_CUDA(cudaStreamWaitEvent(ctx.copy_stream, ctx.ev_sync, 0));
+    Uploader up;
+    const int device = ctx.device;
+    cudaStream_t cs = ctx.copy_stream;
+    cudaEvent_t *evs = ctx.ev_copy;
+    up.th = std::thread([&, device, cs, evs] {
+        bool ok = cudaSetDevice(device) == cudaSuccess;
+        for (size_t k = 0; k < parts && ok; k++) {
+            const size_t lo = lo_of(k), cnt = hi_of(k) - lo;
+            ok = cudaMemcpyAsync((char *)d_sc + lo * sb, (const char *)scalars + lo * sb, cnt * sb,
+                                 cudaMemcpyHostToDevice, cs) == cudaSuccess &&
+                 cudaMemcpyAsync((char *)d_raw + lo * gb, (const char *)bases + lo * gb, cnt * gb,
+                                 cudaMemcpyHostToDevice, cs) == cudaSuccess &&
+                 cudaEventRecord(evs[k], cs) == cudaSuccess;
+            std::lock_guard<std::mutex> lk(up.m);
+            if (ok)
+                up.issued = (int)k + 1;
+            else
+                up.failed = true;
+            up.cv.notify_all();
+        }
+    });
+    if (!mark_all(ctx, PH_INGEST + 1)) return false;
+    for (size_t k = 0; k < parts; k++) {
+        const size_t lo = lo_of(k), cnt = hi_of(k) - lo;
+        up.wait_for((int)k);
+        if (up.failed) return set_error("multi_exp: host to device copy failed"), false;
+        B200_CUDA(cudaStreamWaitEvent(ctx.stream, ctx.ev_copy[k], 0));
+        if (!ops->ingest(ctx, (char *)d_raw + lo * gb, cnt, base_form, (char *)d_aff + lo * ab,
+                         (uint8_t *)d_inf + lo))
+            return false;
+        B200_CUDA(cudaEventRecord(ctx.ev[PH_INGEST + 1], ctx.stream));
+        if (!ops->msm(ctx, (char *)d_aff + lo * ab, (const uint8_t *)d_inf + lo, (char *)d_sc + lo * sb,
+                      cnt, (char *)d_parts + k * gb))
+            return false;
+    }
+    if (!ops->sum(ctx, d_parts, parts, d_out)) return false;
+    return finish_msm(ctx, ops, d_out, out);
 }
 
 bool b200msm_bases_upload(uint32_t group, const void *bases, size_t bases_bytes, size_t n,
@@ -380,6 +472,10 @@ bool b200msm_set_option(const char *name, int64_t value) {
     if (!g_ctx) return set_error("set_option before init"), false;
     if (name && !strcmp(name, "window_bits")) return g_ctx->opt_window_bits = (int)value, true;
     if (name && !strcmp(name, "segment")) return g_ctx->opt_segment = (int)value, true;
+    if (name && !strcmp(name, "h2d_parts")) {
+        if (value < 0 || value > MAX_H2D_PARTS) return set_error("h2d_parts out of range"), false;
+        return g_ctx->opt_h2d_parts = (int)value, true;
+    }
     return set_error("unknown option %s", name ? name : "(null)"), false;
 }
 

@@ -48,6 +48,7 @@ enum Slot {
     SL_CURSOR,
     SL_TILE_SUMS,
     SL_SORTED,
+    SL_SEG_BUCKET,
     SL_BUCKETS,
     SL_CARRY_KEY_A,
     SL_CARRY_PT_A,
@@ -56,6 +57,7 @@ enum Slot {
     SL_CHUNKS,
     SL_WINDOWS,
     SL_OUT,
+    SL_PARTIALS,    // per-range partial results of a pipelined host call
     SL_INV_VAL,
     SL_INV_PRE,
     SL_INV_PROD,
@@ -66,9 +68,14 @@ enum Slot {
     SL_COUNT
 };
 
+constexpr int MAX_H2D_PARTS = 16;
+
 struct Ctx {
     int device = -1;
     cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr;          // host -> device uploads of a pipelined call
+    cudaEvent_t ev_copy[MAX_H2D_PARTS] = {};     // "range k is on the device"
+    cudaEvent_t ev_sync = nullptr;
     void *slot_ptr[SL_COUNT] = {};
     size_t slot_bytes[SL_COUNT] = {};
     cudaEvent_t ev[PH_COUNT + 1] = {};
@@ -77,6 +84,7 @@ struct Ctx {
     uint64_t launches = 0;
     int opt_window_bits = 0;  // 0 = automatic
     int opt_segment = 0;      // 0 = default
+    int opt_h2d_parts = 0;    // 0 = automatic
 
     bool reserve(Slot s, size_t bytes, void **out);
     void release_all();

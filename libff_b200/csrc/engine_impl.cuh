@@ -132,7 +132,7 @@ constexpr int SEG_CARRY = 16;   // carries per thread, later accumulation rounds
 // Sorted entries per thread in the first accumulation round: long segments amortise the carry
 // rounds (one full addition per segment), short ones keep all SMs busy on small inputs.
 inline uint32_t pick_segment(const Ctx &ctx, size_t total) {
-    if (ctx.opt_segment > 0) return (uint32_t)ctx.opt_segment;
+    if (ctx.opt_segment > 0) return ((uint32_t)ctx.opt_segment + 3u) & ~3u;  // uint4 item loads
     const size_t want_threads = 148 * 384 * 4;
     uint32_t seg = 64;
     while (seg > 8 && total / seg < want_threads) seg >>= 1;
@@ -170,7 +170,6 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
     if (!reserve_as(ctx, SL_HIST, M * 4, &hist)) return false;
     if (!reserve_as(ctx, SL_OFFSETS, (M + 1) * 4, &offsets)) return false;
     if (!reserve_as(ctx, SL_CURSOR, M * 4, &cursor)) return false;
-    if (!reserve_as(ctx, SL_SORTED, (size_t)W * n * sizeof(Entry), &sorted)) return false;
     if (!reserve_as(ctx, SL_BUCKETS, M * R::XW * 4, &buckets)) return false;
 
     // --- digits + histogram
@@ -190,27 +189,32 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
     k_scan_apply<<<tiles, SCAN_THREADS, 0, st>>>(hist, tile_sums, tiles, offsets, cursor, (uint32_t)M);
     B200_LAUNCH_CHECK(ctx);
     B200_CUDA(cudaEventRecord(ctx.ev[PH_SCAN + 1], st));
-    // --- scatter
-    k_scatter<C><<<dim3(cdiv(n, 256), W), 256, 0, st>>>(digits, cursor, sorted, (uint32_t)n, c);
-    B200_LAUNCH_CHECK(ctx);
-    B200_CUDA(cudaEventRecord(ctx.ev[PH_SCATTER + 1], st));
-    // the number of sorted entries is known only on the device; it is needed for launch sizing
+    // the number of sorted items is known after the scan; it sizes the accumulation segments
     uint32_t total = 0;
     B200_CUDA(cudaMemcpyAsync(&total, offsets + M, 4, cudaMemcpyDeviceToHost, st));
     B200_CUDA(cudaStreamSynchronize(st));
+    const uint32_t seg = pick_segment(ctx, total);
+    const size_t t1 = ((size_t)total + seg - 1) / seg;
+    uint32_t *seg_bucket;
+    if (!reserve_as(ctx, SL_SEG_BUCKET, (t1 + 1) * 4, &seg_bucket)) return false;
+    // the sorted array is read four items at a time
+    if (!reserve_as(ctx, SL_SORTED, ((size_t)W * n + 4) * sizeof(Entry), &sorted)) return false;
+    // --- scatter
+    k_scatter<C><<<dim3(cdiv(n, 256), W), 256, 0, st>>>(digits, cursor, sorted, seg_bucket,
+                                                       (uint32_t)n, c, seg);
+    B200_LAUNCH_CHECK(ctx);
+    B200_CUDA(cudaEventRecord(ctx.ev[PH_SCATTER + 1], st));
 
     // --- accumulation rounds
     if (total > 0) {
-        const uint32_t seg = pick_segment(ctx, total);
-        size_t t1 = ((size_t)total + seg - 1) / seg;
         size_t t2 = (t1 + SEG_CARRY - 1) / SEG_CARRY;
         uint32_t *keyA, *ptA, *keyB, *ptB;
         if (!reserve_as(ctx, SL_CARRY_KEY_A, t1 * 4, &keyA)) return false;
         if (!reserve_as(ctx, SL_CARRY_PT_A, t1 * R::XW * 4, &ptA)) return false;
         if (!reserve_as(ctx, SL_CARRY_KEY_B, t2 * 4, &keyB)) return false;
         if (!reserve_as(ctx, SL_CARRY_PT_B, t2 * R::XW * 4, &ptB)) return false;
-        k_accum_first<C><<<cdiv(t1, 128), 128, 0, st>>>(sorted, total, seg, (const uint32_t *)d_aff,
-                                                        buckets, keyA, ptA);
+        k_accum_first<C><<<cdiv(t1, 128), 128, 0, st>>>(sorted, offsets, seg_bucket, total, seg,
+                                                        (const uint32_t *)d_aff, buckets, keyA, ptA);
         B200_LAUNCH_CHECK(ctx);
         B200_CUDA(cudaEventRecord(ctx.ev[PH_ACCUM + 1], st));
         size_t len = t1;

@@ -5,7 +5,8 @@
 //   k_digits        scalars: Montgomery -> plain (fp.tcc:270-281) -> signed c-bit digits
 //                   (field_utils.tcc:167-239 restated as a single carry pass) + bucket histogram
 //   k_scan_*        exclusive prefix sum of the histogram -> bucket offsets (3 launches)
-//   k_scatter       counting-sort scatter of (bucket, point index | sign) pairs
+//   k_scatter       counting-sort scatter of (point index | sign) words; also records the bucket
+//                   that owns the first item of every accumulation segment
 //   k_accum_first   balanced segmented accumulation: every thread sums SEG consecutive sorted
 //                   entries with mixed additions (multiexp.tcc:319-345 / :45-81); sums of buckets
 //                   that begin inside the segment are stored, the leading partial becomes a carry
@@ -19,10 +20,10 @@
 
 namespace b200msm {
 
-struct Entry {           // one sorted item: global bucket id, point index with the sign in bit 31
-    uint32_t bucket;
-    uint32_t idx;
-};
+// One sorted item is a 32-bit word: point index with the digit's sign in bit 31.  Its bucket is
+// implied by its position (offsets[b] <= pos < offsets[b + 1]); 4-byte items keep the scatter
+// target of one window (n x 4 B) inside the 126 MB L2, so the random writes combine there.
+typedef uint32_t Entry;
 
 // ------------------------------------------------------------------------------------------
 // bases: reference layout -> device affine (x, y); infinity -> (0, 0) + flag
@@ -158,7 +159,8 @@ static __global__ void __launch_bounds__(SCAN_THREADS)
 // ------------------------------------------------------------------------------------------
 template <class C>
 __global__ void k_scatter(const int32_t *__restrict__ digits, uint32_t *__restrict__ cursor,
-                          Entry *__restrict__ sorted, uint32_t n, int c) {
+                          Entry *__restrict__ sorted, uint32_t *__restrict__ seg_bucket,
+                          uint32_t n, int c, uint32_t SEG) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t w = blockIdx.y;
     if (i >= n) return;
@@ -166,14 +168,19 @@ __global__ void k_scatter(const int32_t *__restrict__ digits, uint32_t *__restri
     if (d == 0) return;
     uint32_t b = (w << (c - 1)) + (uint32_t)(d < 0 ? -d : d) - 1;
     uint32_t pos = atomicAdd(&cursor[b], 1u);
-    sorted[pos] = Entry{b, i | (d < 0 ? 0x80000000u : 0u)};
+    sorted[pos] = i | (d < 0 ? 0x80000000u : 0u);
+    // every position is written exactly once, so exactly one thread sees each segment start
+    if (pos % SEG == 0) seg_bucket[pos / SEG] = b;
 }
 
 // ------------------------------------------------------------------------------------------
-// First accumulation round: thread t owns sorted[t*SEG, (t+1)*SEG) (SEG chosen by the host).
+// First accumulation round: thread t owns sorted[t*SEG, (t+1)*SEG) (SEG chosen by the host, a
+// multiple of 4).  Bucket boundaries come from the offsets array, walked from the segment's
+// first bucket (recorded by the scatter).
 template <class C>
 __global__ void __launch_bounds__(128)
-    k_accum_first(const Entry *__restrict__ sorted, uint32_t total, uint32_t SEG,
+    k_accum_first(const Entry *__restrict__ sorted, const uint32_t *__restrict__ offsets,
+                  const uint32_t *__restrict__ seg_bucket, uint32_t total, uint32_t SEG,
                   const uint32_t *__restrict__ aff, uint32_t *__restrict__ bucket_acc,
                   uint32_t *__restrict__ carry_key, uint32_t *__restrict__ carry_pt) {
     using R = Raw<C>;
@@ -185,21 +192,25 @@ __global__ void __launch_bounds__(128)
     const uint32_t start = (uint32_t)start64;
     const uint32_t end = (uint32_t)min((uint64_t)total, start64 + SEG);
 
-    Entry e = sorted[start];
-    uint32_t cur = e.bucket;
-    bool head_carry = start > 0 && sorted[start - 1].bucket == cur;
+    uint32_t cur = seg_bucket[t];
+    uint32_t next = offsets[cur + 1];            // first position of the following bucket
+    bool head_carry = start > offsets[cur];      // the bucket began in an earlier segment
     carry_key[t] = cur;
     bool carried = false;
     X acc = X::inf();
-    Affine<F> p = Affine<F>::load(aff + (size_t)(e.idx & 0x7fffffffu) * R::AW);
+    uint4 q = *reinterpret_cast<const uint4 *>(sorted + start);  // 4 items per load
+    Entry e = q.x;
+    Affine<F> p = Affine<F>::load(aff + (size_t)(e & 0x7fffffffu) * R::AW);
     for (uint32_t pos = start; pos < end; pos++) {
         const Entry ecur = e;
         const Affine<F> pcur = p;
-        if (pos + 1 < end) {  // prefetch the next entry and point
-            e = sorted[pos + 1];
-            p = Affine<F>::load(aff + (size_t)(e.idx & 0x7fffffffu) * R::AW);
+        if (pos + 1 < end) {  // prefetch the next item and its point
+            const uint32_t k = (pos + 1 - start) & 3u;
+            if (k == 0) q = *reinterpret_cast<const uint4 *>(sorted + pos + 1);
+            e = k == 0 ? q.x : k == 1 ? q.y : k == 2 ? q.z : q.w;
+            p = Affine<F>::load(aff + (size_t)(e & 0x7fffffffu) * R::AW);
         }
-        if (ecur.bucket != cur) {
+        if (pos == next) {  // the run of `cur` is complete; `pos` starts a later, non-empty bucket
             if (head_carry && !carried) {
                 acc.store(carry_pt + (size_t)t * R::XW);
                 carried = true;
@@ -207,10 +218,13 @@ __global__ void __launch_bounds__(128)
                 acc.store(bucket_acc + (size_t)cur * R::XW);
             }
             head_carry = false;
-            cur = ecur.bucket;
+            do {
+                cur++;
+                next = offsets[cur + 1];
+            } while (next <= pos);  // skip empty buckets
             acc = X::inf();
         }
-        X::madd(acc, pcur.x, F::cneg(pcur.y, (ecur.idx >> 31) != 0));
+        X::madd(acc, pcur.x, F::cneg(pcur.y, (ecur >> 31) != 0));
     }
     if (head_carry && !carried) {
         acc.store(carry_pt + (size_t)t * R::XW);

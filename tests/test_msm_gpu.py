@@ -229,3 +229,45 @@ def test_errors(engine):
         engine.multi_exp(0, b, s)
     with pytest.raises(engine.B200MsmError):
         engine.multi_exp(9, b, s)
+
+
+@pytest.mark.parametrize("seg", [3, 4, 12, 64, 256])
+def test_multi_exp_segment_lengths(engine, ref, seg):
+    """Accumulation segment length (items per thread) is a tuning knob: any value gives the same
+    element, including segments that span many small buckets and buckets that span many segments
+    (few distinct scalars -> long runs and multi-round carries)."""
+    gid = 0
+    n = 3000
+    bases = ref.gen_bases_walk(gid, n)
+    scalars = ref.gen_scalars(gid, n, start=11)
+    heavy = np.repeat(ref.gen_scalars(gid, 3, start=5), n // 3, axis=0)  # three huge buckets/window
+    engine.set_option("segment", seg)
+    try:
+        for cbits in (0, 4, 12):
+            engine.set_option("window_bits", cbits)
+            for sc in (scalars, heavy):
+                want = ref.multi_exp(gid, bases, sc)
+                assert_same_point(ref, gid, engine.multi_exp(gid, bases, sc), want)
+    finally:
+        engine.set_option("segment", 0)
+        engine.set_option("window_bits", 0)
+
+
+@pytest.mark.parametrize("gid", GROUPS)
+@pytest.mark.parametrize("parts", [1, 2, 3, 7])
+def test_multi_exp_pipelined_upload(engine, ref, gid, parts):
+    """Host-buffer calls cut the point range into `h2d_parts` independently uploaded and computed
+    ranges (upload of range k + 1 under the MSM of range k); the sum of the partial results is the
+    same element (multiexp.tcc:663-687 does the same split across threads)."""
+    n = {0: 1003, 1: 301, 2: 502, 3: 99}[gid]
+    aff = ref.gen_bases_walk(gid, n + 1)
+    jac = ref.group_op(gid, ref.G_ADD, aff[:-1], aff[1:])
+    scalars = ref.gen_scalars(gid, n, start=21)
+    engine.set_option("h2d_parts", parts)
+    try:
+        assert_same_point(ref, gid, engine.multi_exp(gid, aff[:n], scalars), ref.multi_exp(gid, aff[:n], scalars))
+        assert_same_point(ref, gid, engine.multi_exp(gid, jac, scalars, base_form=engine.FORM_NORMAL),
+                          ref.multi_exp(gid, jac, scalars, form=ref.FORM_NORMAL))
+        assert_same_point(ref, gid, engine.multi_exp(gid, aff[:2], scalars[:2]), ref.multi_exp(gid, aff[:2], scalars[:2]))
+    finally:
+        engine.set_option("h2d_parts", 0)
