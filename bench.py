@@ -259,6 +259,13 @@ def main():
                "ms_per_step": dte / args.steps * 1e3,
                "ingest_ms": float(np.mean([p["ingest"] for p in ph_e])),
                "call": "b200msm_multi_exp(host bases, host scalars) -> host result"}
+        # the same call on pageable memory (what a libff std::vector is): staged through the
+        # engine's pinned ring buffers
+        def step_pageable():
+            return combine(m.multi_exp(gid, bases, scalars))
+
+        dtp, _, _ = timed(step_pageable, max(2, args.steps // 2), 1)
+        e2e["pageable_value"] = n_total / (dtp / max(2, args.steps // 2))
         del hb, hs
 
     if rank != 0:

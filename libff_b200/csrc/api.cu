@@ -146,8 +146,81 @@ size_t pick_parts(const Ctx &ctx, size_t n) {
     return 3;
 }
 
-// Uploads the parts in order on the copy stream from a helper thread (a cudaMemcpyAsync from
-// pageable memory blocks its caller, which must not be the thread that launches the kernels).
+// ---- host -> device uploads ------------------------------------------------------------------
+// Pinned (cudaHostAlloc / cudaHostRegister) sources go straight to cudaMemcpyAsync.  Pageable
+// sources -- what a std::vector<G> of a libff caller is -- would be staged by the driver at
+// ~10 GB/s; instead STAGE_LANES host threads copy slices into the engine's own pinned ring
+// buffers and issue the DMA from there, which keeps the PCIe link busy.
+constexpr int STAGE_LANES = 4;
+constexpr size_t STAGE_BYTES = (size_t)8 << 20;
+
+struct Stager {
+    void *buf[STAGE_LANES][2] = {};
+    cudaEvent_t ev[STAGE_LANES][2] = {};
+    bool ready = false;
+    bool init() {
+        if (ready) return true;
+        for (int l = 0; l < STAGE_LANES; l++)
+            for (int b = 0; b < 2; b++) {
+                B200_CUDA(cudaHostAlloc(&buf[l][b], STAGE_BYTES, cudaHostAllocDefault));
+                B200_CUDA(cudaEventCreateWithFlags(&ev[l][b], cudaEventDisableTiming));
+            }
+        ready = true;
+        return true;
+    }
+    void release() {
+        for (int l = 0; l < STAGE_LANES; l++)
+            for (int b = 0; b < 2; b++) {
+                if (buf[l][b]) cudaFreeHost(buf[l][b]);
+                if (ev[l][b]) cudaEventDestroy(ev[l][b]);
+                buf[l][b] = nullptr;
+                ev[l][b] = nullptr;
+            }
+        ready = false;
+    }
+};
+Stager g_stager;
+
+bool is_pinned(const void *p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeHost || a.type == cudaMemoryTypeManaged;
+}
+
+// Queues the upload of `bytes` bytes on stream `cs`; returns once every DMA has been issued
+// (pageable sources: once the last slice has been copied into a staging buffer).
+bool upload(int device, void *dst, const void *src, size_t bytes, cudaStream_t cs) {
+    if (bytes == 0) return true;
+    if (is_pinned(src) || bytes < STAGE_BYTES)
+        return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, cs) == cudaSuccess;
+    const size_t slices = (bytes + STAGE_BYTES - 1) / STAGE_BYTES;
+    std::atomic<bool> ok{true};
+    std::thread lanes[STAGE_LANES];
+    for (int l = 0; l < STAGE_LANES; l++) {
+        lanes[l] = std::thread([&, l] {
+            if (cudaSetDevice(device) != cudaSuccess) ok = false;
+            int b = 0;
+            for (size_t s = l; s < slices && ok; s += STAGE_LANES, b ^= 1) {
+                const size_t off = s * STAGE_BYTES, len = std::min(STAGE_BYTES, bytes - off);
+                // the previous DMA out of this buffer must have finished
+                if (cudaEventSynchronize(g_stager.ev[l][b]) != cudaSuccess) ok = false;
+                memcpy(g_stager.buf[l][b], (const char *)src + off, len);
+                if (cudaMemcpyAsync((char *)dst + off, g_stager.buf[l][b], len, cudaMemcpyHostToDevice,
+                                    cs) != cudaSuccess ||
+                    cudaEventRecord(g_stager.ev[l][b], cs) != cudaSuccess)
+                    ok = false;
+            }
+        });
+    }
+    for (auto &t : lanes) t.join();
+    return ok;
+}
+
+// Uploads the parts of a pipelined call in order on the copy stream from a helper thread (the
+// staging copies block their caller, which must not be the thread that launches the kernels).
 struct Uploader {
     std::mutex m;
     std::condition_variable cv;
@@ -206,6 +279,7 @@ void b200msm_shutdown(void) {
     }
     g_resident.clear();
     g_ctx->release_all();
+    g_stager.release();
     for (auto &e : g_ctx->ev) cudaEventDestroy(e);
     for (auto &e : g_ctx->ev_copy) cudaEventDestroy(e);
     cudaEventDestroy(g_ctx->ev_sync);
@@ -249,8 +323,10 @@ bool b200msm_multi_exp(uint32_t group, const void *bases, size_t bases_bytes, co
     B200_CUDA(cudaEventRecord(ctx.ev[0], ctx.stream));
     if (parts <= 1) {
         if (n > 0) {
-            B200_CUDA(cudaMemcpyAsync(d_raw, bases, bases_bytes, cudaMemcpyHostToDevice, ctx.stream));
-            B200_CUDA(cudaMemcpyAsync(d_sc, scalars, scalars_bytes, cudaMemcpyHostToDevice, ctx.stream));
+            if (!g_stager.init()) return false;
+            if (!upload(ctx.device, d_raw, bases, bases_bytes, ctx.stream) ||
+                !upload(ctx.device, d_sc, scalars, scalars_bytes, ctx.stream))
+                return set_error("multi_exp: host to device copy failed"), false;
             if (!ops->ingest(ctx, d_raw, n, base_form, d_aff, (uint8_t *)d_inf)) return false;
         }
         return run_msm(ctx, ops, d_aff, (const uint8_t *)d_inf, d_sc, n, out);
@@ -264,6 +340,7 @@ bool b200msm_multi_exp(uint32_t group, const void *bases, size_t bases_bytes, co
     // still in flight: the copy stream starts after everything queued so far
     B200_CUDA(cudaEventRecord(ctx.ev_sync, ctx.stream));
     B200_CUDA(cudaStreamWaitEvent(ctx.copy_stream, ctx.ev_sync, 0));
+    if (!g_stager.init()) return false;
     Uploader up;
     const int device = ctx.device;
     cudaStream_t cs = ctx.copy_stream;
@@ -272,10 +349,8 @@ bool b200msm_multi_exp(uint32_t group, const void *bases, size_t bases_bytes, co
         bool ok = cudaSetDevice(device) == cudaSuccess;
         for (size_t k = 0; k < parts && ok; k++) {
             const size_t lo = lo_of(k), cnt = hi_of(k) - lo;
-            ok = cudaMemcpyAsync((char *)d_sc + lo * sb, (const char *)scalars + lo * sb, cnt * sb,
-                                 cudaMemcpyHostToDevice, cs) == cudaSuccess &&
-                 cudaMemcpyAsync((char *)d_raw + lo * gb, (const char *)bases + lo * gb, cnt * gb,
-                                 cudaMemcpyHostToDevice, cs) == cudaSuccess &&
+            ok = upload(device, (char *)d_sc + lo * sb, (const char *)scalars + lo * sb, cnt * sb, cs) &&
+                 upload(device, (char *)d_raw + lo * gb, (const char *)bases + lo * gb, cnt * gb, cs) &&
                  cudaEventRecord(evs[k], cs) == cudaSuccess;
             std::lock_guard<std::mutex> lk(up.m);
             if (ok)
@@ -317,8 +392,9 @@ bool b200msm_bases_upload(uint32_t group, const void *bases, size_t bases_bytes,
     if (!ctx.reserve(SL_RAW, bases_bytes, &d_raw)) return false;
     B200_CUDA(cudaMalloc(&r.data, n * ops->affine_bytes));
     B200_CUDA(cudaMalloc((void **)&r.inf, n));
-    B200_CUDA(cudaMemcpyAsync(d_raw, bases, bases_bytes, cudaMemcpyHostToDevice, ctx.stream));
-    bool ok = ops->ingest(ctx, d_raw, n, base_form, r.data, r.inf);
+    if (!g_stager.init()) return false;
+    bool ok = upload(ctx.device, d_raw, bases, bases_bytes, ctx.stream) &&
+              ops->ingest(ctx, d_raw, n, base_form, r.data, r.inf);
     if (ok && cudaStreamSynchronize(ctx.stream) != cudaSuccess) ok = false, set_error("ingest failed");
     if (!ok) {
         cudaFree(r.data);

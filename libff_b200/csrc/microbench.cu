@@ -100,6 +100,25 @@ __global__ void k_dfma_imad(double *out, double seed, int iters) {
     out[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
 
+// Random gather of 64-byte records (two uint4 per record), the access pattern of the bucket
+// accumulation; idx = hash of the record number.  Reports useful GB/s.
+__global__ void k_gather64(const uint4 *__restrict__ src, uint4 *__restrict__ dst, uint32_t mask,
+                           uint32_t count) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    uint32_t h = i * 2654435761u;
+    h ^= h >> 15;
+    h *= 2246822519u;
+    h ^= h >> 13;
+    const uint4 *p = src + (size_t)(h & mask) * 4;
+    uint4 a = p[0], b = p[1], c = p[2], d = p[3];
+    a.x ^= b.x ^ c.x ^ d.x;
+    a.y ^= b.y ^ c.y ^ d.y;
+    a.z ^= b.z ^ c.z ^ d.z;
+    a.w ^= b.w ^ c.w ^ d.w;
+    dst[i] = a;
+}
+
 template <class P>
 __global__ void k_mont(uint32_t *out, uint32_t seed, int iters) {
     using F = Fp<P>;
@@ -171,6 +190,19 @@ int main(int argc, char **argv) {
             ms = time_ms([&] { k_mont<Bw6761FqParams><<<blocks, 128>>>((uint32_t *)out, 7, iters / 8); });
             printf(", \"mont24_w%d_Gmul\": %.2f", wps, muls / 8 / ms * 1e-6);
         }
+    }
+    {
+        const uint32_t recs = 1u << 24, count = 1u << 26;  // 1 GiB of 64-byte records
+        uint4 *src, *dst;
+        CK(cudaMalloc(&src, (size_t)recs * 64));
+        CK(cudaMalloc(&dst, (size_t)count * 16));
+        CK(cudaMemset(src, 1, (size_t)recs * 64));
+        for (int gran : {128, 64, 32}) {
+            cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, gran);
+            float ms = time_ms([&] { k_gather64<<<count / 256, 256>>>(src, dst, recs - 1, count); });
+            printf(", \"gather64_l2gran%d_GBps\": %.1f", gran, (double)count * 64 / ms * 1e-6);
+        }
+        cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, 128);
     }
     printf("}\n");
     return 0;
