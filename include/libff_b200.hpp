@@ -9,6 +9,7 @@
  *                                                   multiexp.hpp:63-73, multiexp.tcc:643-688
  *   libff::internal::multi_exp_implementation<G, Fr, Method, Form>::multi_exp_inner
  *                                                   multiexp.tcc:198-212, 276-381, 507-633
+ *   libff::multi_exp_filter_one_zero<G, Fr, Method, Form>   multiexp.hpp:78-88, multiexp.tcc:690-757
  *   libff::batch_exp<G, Fr>(scalar_size, window, table, v[, num_entries])
  *                                                   multiexp.hpp:120-134, multiexp.tcc:875-915
  *   libff::batch_to_special<G>(vec)                 multiexp.hpp:144, multiexp.tcc:949-974
@@ -210,6 +211,20 @@ template<typename GroupT> void batch_to_special(std::vector<GroupT> &vec)
         const size_t chunks)                                                                  \
     {                                                                                         \
         (void)chunks; /* OpenMP split hint of the CPU path, multiexp.tcc:655-687 */           \
+        return b200::multi_exp<G, F>(vec_start, vec_end, scalar_start, scalar_end, FORM);     \
+    }                                                                                         \
+    /* multiexp.tcc:690-757: the CPU pre-pass (skip zeros, add the bases of unit scalars one  \
+       by one) is pointless on the device, where a zero scalar yields no bucket item and a    \
+       unit scalar exactly one */                                                             \
+    template<>                                                                                \
+    inline G multi_exp_filter_one_zero<G, F, METHOD, FORM>(                                   \
+        std::vector<G>::const_iterator vec_start,                                             \
+        std::vector<G>::const_iterator vec_end,                                               \
+        std::vector<F>::const_iterator scalar_start,                                          \
+        std::vector<F>::const_iterator scalar_end,                                            \
+        const size_t chunks)                                                                  \
+    {                                                                                         \
+        (void)chunks;                                                                         \
         return b200::multi_exp<G, F>(vec_start, vec_end, scalar_start, scalar_end, FORM);     \
     }                                                                                         \
     namespace internal                                                                        \

@@ -168,14 +168,15 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
     Entry *sorted;
     if (!reserve_as(ctx, SL_DIGITS, (size_t)W * n * 4, &digits)) return false;
     if (!reserve_as(ctx, SL_HIST, M * 4, &hist)) return false;
-    if (!reserve_as(ctx, SL_OFFSETS, (M + 1) * 4, &offsets)) return false;
+    if (!reserve_as(ctx, SL_OFFSETS, (M + 2) * 4, &offsets)) return false;  // + total, used windows
     if (!reserve_as(ctx, SL_CURSOR, M * 4, &cursor)) return false;
     if (!reserve_as(ctx, SL_BUCKETS, M * R::XW * 4, &buckets)) return false;
 
     // --- digits + histogram
     B200_CUDA(cudaMemsetAsync(hist, 0, M * 4, st));
+    B200_CUDA(cudaMemsetAsync(offsets + M + 1, 0, 4, st));
     k_digits<C><<<cdiv(n, 256), 256, 0, st>>>((const uint32_t *)d_scalars, d_inf, digits, hist,
-                                               (uint32_t)n, c, W);
+                                               offsets + M + 1, (uint32_t)n, c, W);
     B200_LAUNCH_CHECK(ctx);
     B200_CUDA(cudaEventRecord(ctx.ev[PH_DIGITS + 1], st));
     // --- offsets
@@ -190,9 +191,11 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
     B200_LAUNCH_CHECK(ctx);
     B200_CUDA(cudaEventRecord(ctx.ev[PH_SCAN + 1], st));
     // the number of sorted items is known after the scan; it sizes the accumulation segments
-    uint32_t total = 0;
-    B200_CUDA(cudaMemcpyAsync(&total, offsets + M, 4, cudaMemcpyDeviceToHost, st));
+    uint32_t meta[2] = {0, 0};
+    B200_CUDA(cudaMemcpyAsync(meta, offsets + M, 8, cudaMemcpyDeviceToHost, st));
     B200_CUDA(cudaStreamSynchronize(st));
+    const uint32_t total = meta[0];
+    const int Wu = std::max<int>(1, std::min<int>(W, (int)meta[1]));  // windows that hold items
     const uint32_t seg = pick_segment(ctx, total);
     const size_t t1 = ((size_t)total + seg - 1) / seg;
     uint32_t *seg_bucket;
@@ -238,9 +241,9 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
     while ((M / K) > 131072 && K < 128) K <<= 1;
     K = std::min(K, B);
     const uint32_t nchunks = (B + K - 1) / K;
-    if (!reserve_as(ctx, SL_CHUNKS, (size_t)W * nchunks * R::XW * 4, &chunks)) return false;
-    if (!reserve_as(ctx, SL_WINDOWS, (size_t)W * R::XW * 4, &windows)) return false;
-    k_bucket_reduce<C><<<dim3(cdiv(nchunks, 64), W), 64, 0, st>>>(buckets, hist, B, K, chunks);
+    if (!reserve_as(ctx, SL_CHUNKS, (size_t)Wu * nchunks * R::XW * 4, &chunks)) return false;
+    if (!reserve_as(ctx, SL_WINDOWS, (size_t)Wu * R::XW * 4, &windows)) return false;
+    k_bucket_reduce<C><<<dim3(cdiv(nchunks, 64), Wu), 64, 0, st>>>(buckets, hist, B, K, chunks);
     B200_LAUNCH_CHECK(ctx);
     B200_CUDA(cudaEventRecord(ctx.ev[PH_BUCKET_REDUCE + 1], st));
     constexpr int WR_THREADS = 128;
@@ -251,9 +254,9 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wr_smem));
         attr_set = true;
     }
-    k_window_reduce<C, WR_THREADS><<<W, WR_THREADS, wr_smem, st>>>(chunks, nchunks, windows);
+    k_window_reduce<C, WR_THREADS><<<Wu, WR_THREADS, wr_smem, st>>>(chunks, nchunks, windows);
     B200_LAUNCH_CHECK(ctx);
-    k_final<C><<<1, 32, 0, st>>>(windows, W, c, (uint32_t *)d_out);
+    k_final<C><<<1, 32, 0, st>>>(windows, Wu, c, (uint32_t *)d_out);
     B200_LAUNCH_CHECK(ctx);
     B200_CUDA(cudaEventRecord(ctx.ev[PH_FINAL + 1], st));
     return true;

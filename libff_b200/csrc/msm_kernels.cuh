@@ -43,29 +43,59 @@ __global__ void k_ingest_special(const uint32_t *__restrict__ raw, uint32_t *__r
 }
 
 // ------------------------------------------------------------------------------------------
+// Warp-aggregated counter updates: lanes that hit the same bucket (witness-like inputs put a
+// large share of all scalars into one bucket) issue ONE atomic between them.  Must be called by
+// all 32 lanes.
+__device__ __forceinline__ void warp_hist_add(uint32_t *hist, bool valid, uint32_t bucket) {
+    const uint32_t lane = threadIdx.x & 31;
+    if (!__any_sync(0xffffffffu, valid)) return;  // e.g. the windows above short scalars
+    const uint32_t peers = __match_any_sync(0xffffffffu, valid ? bucket : 0xffffffe0u + lane);
+    if (valid && lane == (uint32_t)__ffs(peers) - 1) atomicAdd(&hist[bucket], (uint32_t)__popc(peers));
+}
+// returns this lane's slot: base of the group's reservation + rank inside the group
+__device__ __forceinline__ uint32_t warp_cursor_take(uint32_t *cursor, bool valid, uint32_t bucket) {
+    const uint32_t lane = threadIdx.x & 31;
+    if (!__any_sync(0xffffffffu, valid)) return 0;
+    const uint32_t peers = __match_any_sync(0xffffffffu, valid ? bucket : 0xffffffe0u + lane);
+    const uint32_t leader = (uint32_t)__ffs(peers) - 1;
+    uint32_t base = 0;
+    if (valid && lane == leader) base = atomicAdd(&cursor[bucket], (uint32_t)__popc(peers));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    return base + (uint32_t)__popc(peers & ((1u << lane) - 1));
+}
+
+// ------------------------------------------------------------------------------------------
 // scalars -> signed digits + histogram.  digits[w * n + i] in [-2^(c-1), 2^(c-1)]
 template <class C>
 __global__ void k_digits(const uint32_t *__restrict__ scalars, const uint8_t *__restrict__ inf_flag,
-                         int32_t *__restrict__ digits, uint32_t *__restrict__ hist, uint32_t n,
-                         int c, int W) {
+                         int32_t *__restrict__ digits, uint32_t *__restrict__ hist,
+                         uint32_t *__restrict__ used_windows, uint32_t n, int c, int W) {
     using Fr = typename C::Fr;
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    Fr s = Fr::from_mont(Fr::load(scalars + (size_t)i * Fr::N));
-    bool skip = inf_flag != nullptr && inf_flag[i];
-    const uint32_t mask = (1u << c) - 1, half = 1u << (c - 1);
-    uint32_t carry = 0;
-    for (int w = 0; w < W; w++) {
-        uint32_t d = (s.v[0] & mask) + carry;
-        carry = d > half;
-        int32_t sd = (int32_t)d - (int32_t)(carry << c);
-        if (skip) sd = 0;
-        digits[(size_t)w * n + i] = sd;
-        if (sd != 0) atomicAdd(&hist[(size_t)w * half + (sd < 0 ? -sd : sd) - 1], 1u);
+    uint32_t top = 0;  // 1 + index of the highest window with a non-zero digit
+    {
+        const bool live = i < n;  // every lane runs the loop: the histogram update is warp-wide
+        Fr s = live ? Fr::from_mont(Fr::load(scalars + (size_t)i * Fr::N)) : Fr::zero();
+        bool skip = !live || (inf_flag != nullptr && inf_flag[i]);
+        const uint32_t mask = (1u << c) - 1, half = 1u << (c - 1);
+        uint32_t carry = 0;
+        for (int w = 0; w < W; w++) {
+            uint32_t d = (s.v[0] & mask) + carry;
+            carry = d > half;
+            int32_t sd = (int32_t)d - (int32_t)(carry << c);
+            if (skip) sd = 0;
+            if (live) digits[(size_t)w * n + i] = sd;
+            if (sd != 0) top = w + 1;
+            warp_hist_add(hist, sd != 0, (uint32_t)w * half + (uint32_t)(sd < 0 ? -sd : sd) - 1);
 #pragma unroll
-        for (int k = 0; k < Fr::N - 1; k++) s.v[k] = __funnelshift_r(s.v[k], s.v[k + 1], c);
-        s.v[Fr::N - 1] >>= c;
+            for (int k = 0; k < Fr::N - 1; k++) s.v[k] = __funnelshift_r(s.v[k], s.v[k + 1], c);
+            s.v[Fr::N - 1] >>= c;
+        }
     }
+    // the reference sizes its loop by the longest scalar (num_bits, multiexp.tcc:298-306); here
+    // the windows above the highest non-zero digit are dropped from the reduction phases
+    top = __reduce_max_sync(0xffffffffu, top);
+    if ((threadIdx.x & 31) == 0 && top > 0) atomicMax(used_windows, top);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -163,11 +193,10 @@ __global__ void k_scatter(const int32_t *__restrict__ digits, uint32_t *__restri
                           uint32_t n, int c, uint32_t SEG) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t w = blockIdx.y;
-    if (i >= n) return;
-    int32_t d = digits[(size_t)w * n + i];
+    const int32_t d = i < n ? digits[(size_t)w * n + i] : 0;
+    const uint32_t b = (w << (c - 1)) + (uint32_t)(d < 0 ? -d : d) - 1;
+    const uint32_t pos = warp_cursor_take(cursor, d != 0, b);  // all lanes take part
     if (d == 0) return;
-    uint32_t b = (w << (c - 1)) + (uint32_t)(d < 0 ? -d : d) - 1;
-    uint32_t pos = atomicAdd(&cursor[b], 1u);
     sorted[pos] = i | (d < 0 ? 0x80000000u : 0u);
     // every position is written exactly once, so exactly one thread sees each segment start
     if (pos % SEG == 0) seg_bucket[pos / SEG] = b;

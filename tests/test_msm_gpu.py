@@ -271,3 +271,23 @@ def test_multi_exp_pipelined_upload(engine, ref, gid, parts):
         assert_same_point(ref, gid, engine.multi_exp(gid, aff[:2], scalars[:2]), ref.multi_exp(gid, aff[:2], scalars[:2]))
     finally:
         engine.set_option("h2d_parts", 0)
+
+
+@pytest.mark.parametrize("gid", GROUPS)
+def test_multi_exp_groth16_shaped_scalars(engine, ref, gid):
+    """Witness-like scalars (what multi_exp_filter_one_zero, multiexp.tcc:690-757, is written for):
+    mostly 0 and 1, some short, few full-width.  Zero scalars give no bucket items, unit scalars
+    pile into one bucket of the lowest window, and the windows above the longest scalar are
+    dropped from the reduction (the reference sizes its loop by num_bits, multiexp.tcc:298-306)."""
+    g = pm.GROUPS[gid]
+    n = {0: 2000, 1: 400, 2: 800, 3: 150}[gid]
+    rng = np.random.RandomState(5 + gid)
+    kinds = rng.choice(4, size=n, p=[0.55, 0.3, 0.1, 0.05])
+    full = g.decode_scalars(ref.gen_scalars(gid, n, start=300))
+    vals = [0 if k == 0 else 1 if k == 1 else int(rng.randint(2, 1 << 16)) if k == 2 else full[i]
+            for i, k in enumerate(kinds)]
+    bases = ref.gen_bases_walk(gid, n)
+    for sc in (vals, [v if k != 3 else 0 for v, k in zip(vals, kinds)], [1] * n, [0] * (n - 1) + [3]):
+        scalars = g.encode_scalars(sc)
+        want = ref.multi_exp(gid, bases, scalars)
+        assert_same_point(ref, gid, engine.multi_exp(gid, bases, scalars), want)
