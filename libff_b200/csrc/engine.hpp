@@ -55,6 +55,7 @@ enum Slot {
     SL_CARRY_KEY_B,
     SL_CARRY_PT_B,
     SL_CHUNKS,
+    SL_CHUNK_TOTALS,
     SL_WINDOWS,
     SL_OUT,
     SL_PARTIALS,    // per-range partial results of a pipelined host call
@@ -85,6 +86,7 @@ struct Ctx {
     int opt_window_bits = 0;  // 0 = automatic
     int opt_segment = 0;      // 0 = default
     int opt_h2d_parts = 0;    // 0 = automatic
+    int opt_reduce_chunk = 0; // log2 of the buckets per thread in the reduction; 0 = automatic
 
     bool reserve(Slot s, size_t bytes, void **out);
     void release_all();

@@ -236,17 +236,22 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
     }
     B200_CUDA(cudaEventRecord(ctx.ev[PH_CARRY + 1], st));
 
-    // --- bucket reduction
+    // --- bucket reduction (B and K are powers of two, K <= B)
     uint32_t K = 16;
-    while ((M / K) > 131072 && K < 128) K <<= 1;
+    while ((M / K) > 65536 && K < 128) K <<= 1;
+    if (ctx.opt_reduce_chunk > 0) K = 1u << std::min(ctx.opt_reduce_chunk, 12);
     K = std::min(K, B);
-    const uint32_t nchunks = (B + K - 1) / K;
+    const uint32_t nchunks = B / K;
+    uint32_t log2K = 0;
+    while ((1u << log2K) < K) log2K++;
+    uint32_t *chunk_T;
     if (!reserve_as(ctx, SL_CHUNKS, (size_t)Wu * nchunks * R::XW * 4, &chunks)) return false;
+    if (!reserve_as(ctx, SL_CHUNK_TOTALS, (size_t)Wu * nchunks * R::XW * 4, &chunk_T)) return false;
     if (!reserve_as(ctx, SL_WINDOWS, (size_t)Wu * R::XW * 4, &windows)) return false;
-    k_bucket_reduce<C><<<dim3(cdiv(nchunks, 64), Wu), 64, 0, st>>>(buckets, hist, B, K, chunks);
+    k_bucket_reduce<C><<<dim3(cdiv(nchunks, 64), Wu), 64, 0, st>>>(buckets, hist, B, K, chunks, chunk_T);
     B200_LAUNCH_CHECK(ctx);
     B200_CUDA(cudaEventRecord(ctx.ev[PH_BUCKET_REDUCE + 1], st));
-    constexpr int WR_THREADS = 128;
+    constexpr int WR_THREADS = 256;
     const size_t wr_smem = (size_t)WR_THREADS * R::XW * 4;
     static bool attr_set = false;
     if (!attr_set) {
@@ -254,7 +259,8 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wr_smem));
         attr_set = true;
     }
-    k_window_reduce<C, WR_THREADS><<<Wu, WR_THREADS, wr_smem, st>>>(chunks, nchunks, windows);
+    k_window_reduce<C, WR_THREADS><<<Wu, WR_THREADS, wr_smem, st>>>(chunks, chunk_T, nchunks, log2K,
+                                                                   windows);
     B200_LAUNCH_CHECK(ctx);
     k_final<C><<<1, 32, 0, st>>>(windows, Wu, c, (uint32_t *)d_out);
     B200_LAUNCH_CHECK(ctx);

@@ -320,21 +320,26 @@ __device__ __noinline__ XYZZ<F> small_mul(const XYZZ<F> &p, uint32_t k) {
     return r;
 }
 
-// Thread (w, j) reduces buckets [j*K, (j+1)*K) of window w:
-//   sum_{b} (j*K + b + 1) * bucket[b]  =  (running sums)  +  (j*K) * (chunk total)
-// B = buckets per window; grid.x covers B/K chunks, grid.y = windows.
+// Bucket reduction in two levels of running sums (multiexp.tcc:90-125, 354-376 is the serial
+// form).  With chunks of K buckets and (b + 1) = (b - jK + 1) + jK:
+//   window sum = sum_j L_j + K * sum_j j T_j,   L_j = sum_{b in chunk j} (b - jK + 1) bucket[b],
+//                                               T_j = sum_{b in chunk j} bucket[b].
+// Level 1 (k_bucket_reduce): thread (w, j) walks its K buckets from the top; `running` ends as
+// T_j and `acc` as L_j -- two additions per bucket, no scalar multiplication.
+// B = buckets per window (a power of two), K a power of two <= B; grid.y = windows.
 template <class C>
 __global__ void __launch_bounds__(64)
     k_bucket_reduce(const uint32_t *__restrict__ bucket_acc, const uint32_t *__restrict__ hist,
-                    uint32_t B, uint32_t K, uint32_t *__restrict__ chunk_sums) {
+                    uint32_t B, uint32_t K, uint32_t *__restrict__ chunk_L,
+                    uint32_t *__restrict__ chunk_T) {
     using R = Raw<C>;
     using F = typename C::Fq;
     using X = XYZZ<F>;
-    const uint32_t chunks = (B + K - 1) / K;
+    const uint32_t chunks = B / K;
     const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t w = blockIdx.y;
     if (j >= chunks) return;
-    const uint32_t lo = j * K, hi = min(B, lo + K);
+    const uint32_t lo = j * K, hi = lo + K;
     X running = X::inf(), acc = X::inf();
     for (uint32_t b = hi; b-- > lo;) {
         const size_t g = (size_t)w * B + b;
@@ -344,58 +349,114 @@ __global__ void __launch_bounds__(64)
         }
         X::add(acc, running);
     }
-    X off = small_mul<F>(running, lo);
-    X::add(acc, off);
-    acc.store(chunk_sums + ((size_t)w * chunks + j) * R::XW);
+    acc.store(chunk_L + ((size_t)w * chunks + j) * R::XW);
+    running.store(chunk_T + ((size_t)w * chunks + j) * R::XW);
 }
 
-// One block per window: total of its chunk sums (strided per thread, then a shared-memory tree).
+// Level 2, one block per window: thread t owns Q consecutive chunks (Q a power of two) and the
+// same trick gives  sum_j j T_j = sum_t A_t + Q * sum_t t R_t  with  R_t = sum_j T_j and
+// A_t = sum_j (j - tQ) T_j over its chunks.  The remaining weights t < THREADS are applied with a
+// short double-and-add in parallel; K and Q are powers of two, i.e. doublings.  A shared-memory
+// tree then adds the THREADS partial results.
 template <class C, int THREADS>
 __global__ void __launch_bounds__(THREADS)
-    k_window_reduce(const uint32_t *__restrict__ chunk_sums, uint32_t chunks,
-                    uint32_t *__restrict__ window_sums) {
+    k_window_reduce(const uint32_t *__restrict__ chunk_L, const uint32_t *__restrict__ chunk_T,
+                    uint32_t chunks, uint32_t log2K, uint32_t *__restrict__ window_sums) {
     using R = Raw<C>;
     using F = typename C::Fq;
     using X = XYZZ<F>;
     extern __shared__ uint32_t smem[];
     const uint32_t w = blockIdx.x, t = threadIdx.x;
-    X acc = X::inf();
-    for (uint32_t j = t; j < chunks; j += THREADS) {
-        X q = X::load(chunk_sums + ((size_t)w * chunks + j) * R::XW);
-        X::add(acc, q);
+    const uint32_t Q = chunks > (uint32_t)THREADS ? chunks / THREADS : 1u;
+    const uint32_t log2Q = 31 - __clz(Q);
+    X total = X::inf();
+    if (t * Q < chunks) {
+        X sumL = X::inf(), run = X::inf(), acc = X::inf();
+        for (uint32_t j = (t + 1) * Q; j-- > t * Q;) {
+            const size_t g = ((size_t)w * chunks + j) * R::XW;
+            X::add(acc, run);  // T_j is counted (j - tQ) times: once per later step
+            X q = X::load(chunk_T + g);
+            X::add(run, q);
+            q = X::load(chunk_L + g);
+            X::add(sumL, q);
+        }
+        X y = small_mul<F>(run, t);
+        for (uint32_t k = 0; k < log2Q; k++) y = X::dbl(y);
+        X::add(y, acc);
+        for (uint32_t k = 0; k < log2K; k++) y = X::dbl(y);
+        total = sumL;
+        X::add(total, y);
     }
-    acc.store(smem + (size_t)t * R::XW);
+    total.store(smem + (size_t)t * R::XW);
     __syncthreads();
     for (uint32_t d = THREADS / 2; d > 0; d >>= 1) {
         if (t < d) {
             X q = X::load(smem + (size_t)(t + d) * R::XW);
-            X::add(acc, q);
-            acc.store(smem + (size_t)t * R::XW);
+            X::add(total, q);
+            total.store(smem + (size_t)t * R::XW);
         }
         __syncthreads();
     }
-    if (t == 0) acc.store(window_sums + (size_t)w * R::XW);
+    if (t == 0) total.store(window_sums + (size_t)w * R::XW);
 }
 
-// result = sum_w 2^(w c) window_sums[w]  (+ optional previous partial), written both as XYZZ and
-// in the reference's coordinate system.
+// One doubling shared by the lanes of a warp.  The c doublings between windows are a serial
+// chain (254..377 in total) that one thread walks at one multiplication latency after the other;
+// the nine products of dbl-2008-s-1 have depth three, so lanes 0..3 take one product each per
+// level and exchange results through shared memory: 3 product latencies per doubling instead
+// of 9.  Every lane holds the full point before and after.  `sh` has 4 * F::N words.
+template <class F>
+__device__ __forceinline__ XYZZ<F> dbl_coop(const XYZZ<F> &p, uint32_t *sh, uint32_t lane) {
+    const uint32_t slot = (lane & 3u) * F::N;
+    const F U = F::dbl(p.Y);
+    // level 1: V = U^2, xx = X^2
+    F t = F::mul(F::select(lane == 1, p.X, U), F::select(lane == 1, p.X, U));
+    __syncwarp();
+    if (lane < 4) t.store(sh + slot);
+    __syncwarp();
+    const F V = F::load(sh), xx = F::load(sh + F::N);
+    const F M = F::add(F::dbl(xx), xx);
+    // level 2: W = U V, S = X V, M^2, ZZ' = V ZZ
+    t = F::mul(lane == 0 ? U : lane == 1 ? p.X : lane == 2 ? M : V,
+               lane == 0 ? V : lane == 1 ? V : lane == 2 ? M : p.ZZ);
+    __syncwarp();
+    if (lane < 4) t.store(sh + slot);
+    __syncwarp();
+    const F Wv = F::load(sh), S = F::load(sh + F::N), MM = F::load(sh + 2 * F::N),
+            ZZ3 = F::load(sh + 3 * F::N);
+    const F X3 = F::sub(MM, F::dbl(S));
+    // level 3: M (S - X3), W Y, ZZZ' = W ZZZ
+    t = F::mul(lane == 0 ? M : Wv, lane == 0 ? F::sub(S, X3) : lane == 1 ? p.Y : p.ZZZ);
+    __syncwarp();
+    if (lane < 4) t.store(sh + slot);
+    __syncwarp();
+    const F Y3 = F::sub(F::load(sh), F::load(sh + F::N));
+    return XYZZ<F>{X3, Y3, ZZ3, F::load(sh + 2 * F::N)};
+}
+
+// result = sum_w 2^(w c) window_sums[w] (Horner from the top window, multiexp.tcc:309-314),
+// written in the reference's coordinate system.  One warp; see dbl_coop.
 template <class C>
-__global__ void k_final(const uint32_t *__restrict__ window_sums, int W, int c,
-                        uint32_t *__restrict__ out_raw) {
+__global__ void __launch_bounds__(32) k_final(const uint32_t *__restrict__ window_sums, int W, int c,
+                                              uint32_t *__restrict__ out_raw) {
     using R = Raw<C>;
     using F = typename C::Fq;
     using X = XYZZ<F>;
-    if (blockIdx.x != 0 || threadIdx.x != 0) return;
+    __shared__ __align__(16) uint32_t sh[4 * F::N];
+    if (blockIdx.x != 0) return;
+    const uint32_t lane = threadIdx.x & 31;
     X r = X::inf();
     for (int w = W - 1; w >= 0; w--) {
-        if (!r.is_inf())
-            for (int k = 0; k < c; k++) r = X::dbl(r);
+        if (!r.is_inf())  // uniform across the warp: every lane holds the same point
+            for (int k = 0; k < c; k++) r = dbl_coop<F>(r, sh, lane);
         X q = X::load(window_sums + (size_t)w * R::XW);
         X::add(r, q);
     }
-    F Xo, Yo, Zo;
-    R::from_xyzz(r, Xo, Yo, Zo);
-    R::store(out_raw, Xo, Yo, Zo);
+    if (lane == 0) {
+        F Xo, Yo, Zo;
+        R::from_xyzz(r, Xo, Yo, Zo);
+        R::store(out_raw, Xo, Yo, Zo);
+    }
 }
 
 // Sum of `count` reference-layout group elements (partials of the GPU shards, multiexp.tcc:681-685)
