@@ -80,6 +80,20 @@ bool b200msm_multi_exp_resident(uint32_t group, uint64_t bases_handle, uint64_t 
                                 size_t first, size_t n, void *out, size_t out_bytes);
 bool b200msm_release(uint64_t handle);
 
+/* The same MSM on the byte format of the reference's C ABI (ffi/ffi_serialization.hpp:12-16,
+ * ffi/ffi_serialization.tcc:98-187; sizes ffi/ffi.h:13-17,55-59) for callers that are not C++:
+ * every base-field value big-endian, left-padded to the in-memory width, plain (not Montgomery);
+ * Fq2 as c1 | c0; a point is affine X | Y (b200msm_wire_point_bytes(group) bytes: 64 / 128 / 96 /
+ * 192) with (0, 1) for infinity; a scalar is sizeof(Fr) bytes.  Decoding, validation and encoding
+ * run on the device.  Like the reference's readers the call fails when a value is >= its modulus;
+ * flags add the point checks of group_element_read (ffi_serialization.tcc:165). */
+#define B200MSM_WIRE_CHECK_CURVE 1u    /* is_well_formed(): y^2 = x^3 + b */
+#define B200MSM_WIRE_CHECK_SUBGROUP 2u /* is_in_safe_subgroup(): r P = 0 (n scalar multiplications) */
+size_t b200msm_wire_point_bytes(uint32_t group);
+bool b200msm_multi_exp_wire(uint32_t group, const void *points, size_t points_bytes,
+                            const void *scalars, size_t scalars_bytes, size_t n, uint32_t flags,
+                            void *out, size_t out_bytes);
+
 /* Sum of `count` group elements in reference layout: the reduction of per-chunk partials that
  * ends libff::multi_exp (multiexp.tcc:681-685); used to combine the partial results of GPU
  * shards.  points_bytes == count * sizeof(GroupT). */

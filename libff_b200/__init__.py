@@ -29,7 +29,8 @@ __all__ = [
     "FORM_NORMAL", "FORM_SPECIAL", "B200MsmError", "lib_path", "load", "init", "shutdown",
     "group_bytes", "scalar_bytes", "multi_exp", "batch_exp", "batch_to_special", "group_sum",
     "ResidentBases", "ResidentScalars", "multi_exp_resident", "last_timings", "launch_count",
-    "set_option", "window_bits", "shard_range",
+    "set_option", "window_bits", "shard_range", "multi_exp_wire", "wire_point_bytes",
+    "WIRE_CHECK_CURVE", "WIRE_CHECK_SUBGROUP",
 ]
 
 ALT_BN128_G1, ALT_BN128_G2, BLS12_377_G1, BW6_761_G1 = 0, 1, 2, 3
@@ -43,6 +44,7 @@ ABI_SYMBOLS = [
     "b200msm_scalars_upload", "b200msm_multi_exp_resident", "b200msm_release", "b200msm_sum",
     "b200msm_batch_to_special", "b200msm_batch_exp", "b200msm_debug_op", "b200msm_set_option",
     "b200msm_last_timings", "b200msm_timing_name", "b200msm_launch_count", "b200msm_window_bits",
+    "b200msm_wire_point_bytes", "b200msm_multi_exp_wire",
 ]
 
 
@@ -91,6 +93,8 @@ def load():
         "b200msm_timing_name": (C.c_char_p, [sz]),
         "b200msm_launch_count": (u64, []),
         "b200msm_window_bits": (u32, [u32, sz]),
+        "b200msm_wire_point_bytes": (sz, [u32]),
+        "b200msm_multi_exp_wire": (C.c_bool, [u32, vp, sz, vp, sz, sz, u32, vp, sz]),
     }
     for name, (res, args) in sigs.items():
         f = getattr(L, name)
@@ -196,6 +200,35 @@ def multi_exp_host_ptr(group: int, bases_ptr: int, scalars_ptr: int, n: int,
                                     n * sb, n, base_form, _ptr(out), out.nbytes):
         _fail("b200msm_multi_exp")
     return out
+
+
+WIRE_CHECK_CURVE, WIRE_CHECK_SUBGROUP = 1, 2
+
+
+def wire_point_bytes(group: int) -> int:
+    return int(load().b200msm_wire_point_bytes(group))
+
+
+def multi_exp_wire(group: int, points: bytes, scalars: bytes, flags: int = WIRE_CHECK_CURVE) -> bytes:
+    """MSM on the byte format of the reference's ffi layer (ffi/ffi_serialization.hpp:12-16): affine
+    big-endian plain X | Y points ((0, 1) = infinity) and big-endian plain scalars; returns the
+    affine result in the same format.  Raises on malformed input, as the reference's readers
+    return false (ffi_serialization.tcc:64-75,165)."""
+    _ensure_init()
+    pb, sb = wire_point_bytes(group), scalar_bytes(group)
+    if pb == 0:
+        raise B200MsmError(f"unknown group id {group}")
+    if len(points) % pb or len(scalars) % sb or len(points) // pb != len(scalars) // sb:
+        raise B200MsmError("multi_exp_wire: buffer sizes do not describe the same number of elements")
+    n = len(points) // pb
+    pa = np.frombuffer(points, dtype=np.uint8)
+    sa = np.frombuffer(scalars, dtype=np.uint8)
+    out = np.zeros(pb, dtype=np.uint8)
+    if not load().b200msm_multi_exp_wire(group, pa.ctypes.data if n else None, pa.nbytes,
+                                         sa.ctypes.data if n else None, sa.nbytes, n, flags,
+                                         out.ctypes.data, out.nbytes):
+        _fail("b200msm_multi_exp_wire")
+    return out.tobytes()
 
 
 def group_sum(group: int, points) -> np.ndarray:

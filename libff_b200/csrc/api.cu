@@ -378,6 +378,57 @@ bool b200msm_multi_exp(uint32_t group, const void *bases, size_t bases_bytes, co
     return finish_msm(ctx, ops, d_out, out);
 }
 
+size_t b200msm_wire_point_bytes(uint32_t group) {
+    const GroupOps *o = ops_for(group);
+    return o ? o->affine_bytes : 0;
+}
+
+bool b200msm_multi_exp_wire(uint32_t group, const void *points, size_t points_bytes,
+                            const void *scalars, size_t scalars_bytes, size_t n, uint32_t flags,
+                            void *out, size_t out_bytes) {
+    std::lock_guard<std::mutex> lk(g_mutex);
+    const GroupOps *ops = checked_ops(group);
+    if (!ops || !ready()) return false;
+    const size_t pb = ops->affine_bytes, sb = ops->scalar_bytes;
+    if (flags > 3) return set_error("multi_exp_wire: unknown flags %u", flags), false;
+    if (points_bytes != n * pb || scalars_bytes != n * sb || out_bytes != pb)
+        return set_error("multi_exp_wire: buffer sizes do not match n = %zu", n), false;
+    if (!out || (n > 0 && (!points || !scalars))) return set_error("multi_exp_wire: null buffer"), false;
+    Ctx &ctx = *g_ctx;
+    void *d_wp, *d_ws, *d_aff, *d_inf, *d_sc, *d_out, *d_misc;
+    if (!ctx.reserve(SL_WIRE_IN, points_bytes, &d_wp)) return false;
+    if (!ctx.reserve(SL_WIRE_SC, scalars_bytes, &d_ws)) return false;
+    if (!ctx.reserve(SL_AFF, n * ops->affine_bytes, &d_aff)) return false;
+    if (!ctx.reserve(SL_INF, n, &d_inf)) return false;
+    if (!ctx.reserve(SL_SCALARS, scalars_bytes, &d_sc)) return false;
+    if (!ctx.reserve(SL_OUT, ops->group_bytes, &d_out)) return false;
+    if (!ctx.reserve(SL_WIRE_MISC, 16 + pb, &d_misc)) return false;
+    uint32_t *d_err = (uint32_t *)d_misc;
+    void *d_wire_out = (char *)d_misc + 16;
+    B200_CUDA(cudaEventRecord(ctx.ev[0], ctx.stream));
+    if (!g_stager.init()) return false;
+    if (!upload(ctx.device, d_wp, points, points_bytes, ctx.stream) ||
+        !upload(ctx.device, d_ws, scalars, scalars_bytes, ctx.stream))
+        return set_error("multi_exp_wire: host to device copy failed"), false;
+    if (!ops->wire_decode(ctx, d_wp, d_ws, n, flags, d_aff, (uint8_t *)d_inf, d_sc, d_err)) return false;
+    uint32_t err = 0;
+    B200_CUDA(cudaMemcpyAsync(&err, d_err, 4, cudaMemcpyDeviceToHost, ctx.stream));
+    B200_CUDA(cudaStreamSynchronize(ctx.stream));
+    if (err)  // the reference's readers return false (ffi_serialization.tcc:64-75,165)
+        return set_error("multi_exp_wire: invalid input (%s%s%s)", err & 1 ? "value >= modulus " : "",
+                         err & 2 ? "point not on curve " : "", err & 4 ? "point not in subgroup" : ""),
+               false;
+    if (!mark_all(ctx, PH_INGEST + 1)) return false;
+    if (!ops->msm(ctx, d_aff, (const uint8_t *)d_inf, d_sc, n, d_out)) return false;
+    if (!ops->wire_encode(ctx, d_out, d_wire_out)) return false;
+    std::vector<unsigned char> tmp(pb);
+    B200_CUDA(cudaMemcpyAsync(tmp.data(), d_wire_out, pb, cudaMemcpyDeviceToHost, ctx.stream));
+    if (!collect_timings(ctx)) return false;
+    B200_CUDA(cudaStreamSynchronize(ctx.stream));
+    memcpy(out, tmp.data(), pb);
+    return true;
+}
+
 bool b200msm_bases_upload(uint32_t group, const void *bases, size_t bases_bytes, size_t n,
                           uint32_t base_form, uint64_t *handle) {
     std::lock_guard<std::mutex> lk(g_mutex);

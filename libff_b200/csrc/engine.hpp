@@ -66,6 +66,9 @@ enum Slot {
     SL_TABLE_AFF,
     SL_TABLE_INF,
     SL_BEXP_OUT,
+    SL_WIRE_IN,
+    SL_WIRE_SC,
+    SL_WIRE_MISC,
     SL_COUNT
 };
 
@@ -115,6 +118,10 @@ struct GroupOps {
     bool (*batch_exp)(Ctx &, const void *d_table_raw, size_t rows, size_t row_len, int window,
                       const void *d_scalars, size_t n, void *d_out);
     uint32_t (*window_bits)(const Ctx &, size_t n);
+    // wire format of the reference's ffi layer (wire_kernels.cuh): decode + validate, encode
+    bool (*wire_decode)(Ctx &, const void *d_wire_points, const void *d_wire_scalars, size_t n,
+                        uint32_t flags, void *d_aff, uint8_t *d_inf, void *d_scalars, uint32_t *d_err);
+    bool (*wire_encode)(Ctx &, const void *d_raw, void *d_wire_out);
     // element-wise leaf operation (debug_kernels.cuh); returns bytes per element via elem_bytes
     bool (*debug_op)(Ctx &, int op, const void *d_a, const void *d_b, void *d_out, size_t n);
     size_t (*debug_elem_bytes)(int op);

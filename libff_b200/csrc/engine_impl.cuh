@@ -6,6 +6,7 @@
 #include "debug_kernels.cuh"
 #include "engine.hpp"
 #include "msm_kernels.cuh"
+#include "wire_kernels.cuh"
 
 namespace b200msm {
 
@@ -293,6 +294,27 @@ uint32_t window_bits_impl(const Ctx &ctx, size_t n) {
 }
 
 template <class C>
+bool wire_decode_impl(Ctx &ctx, const void *d_wire_points, const void *d_wire_scalars, size_t n,
+                      uint32_t flags, void *d_aff, uint8_t *d_inf, void *d_scalars, uint32_t *d_err) {
+    B200_CUDA(cudaMemsetAsync(d_err, 0, 4, ctx.stream));
+    if (n == 0) return true;
+    k_wire_decode_points<C><<<cdiv(n, 128), 128, 0, ctx.stream>>>(
+        (const uint8_t *)d_wire_points, (uint32_t *)d_aff, d_inf, d_err, (uint32_t)n, flags);
+    B200_LAUNCH_CHECK(ctx);
+    k_wire_decode_scalars<C><<<cdiv(n, 256), 256, 0, ctx.stream>>>(
+        (const uint8_t *)d_wire_scalars, (uint32_t *)d_scalars, d_err, (uint32_t)n);
+    B200_LAUNCH_CHECK(ctx);
+    return true;
+}
+
+template <class C>
+bool wire_encode_impl(Ctx &ctx, const void *d_raw, void *d_wire_out) {
+    k_wire_encode_point<C><<<1, 32, 0, ctx.stream>>>((const uint32_t *)d_raw, (uint8_t *)d_wire_out);
+    B200_LAUNCH_CHECK(ctx);
+    return true;
+}
+
+template <class C>
 size_t debug_elem_bytes_impl(int op) {
     using R = Raw<C>;
     if (op <= DBG_FQ_INV) return (size_t)R::CW * 4;
@@ -324,6 +346,8 @@ const GroupOps *make_ops() {
                                  &to_special_impl<C>,
                                  &batch_exp_impl<C>,
                                  &window_bits_impl<C>,
+                                 &wire_decode_impl<C>,
+                                 &wire_encode_impl<C>,
                                  &debug_op_impl<C>,
                                  &debug_elem_bytes_impl<C>};
     return &ops;

@@ -421,3 +421,51 @@ def signed_digits(v: int, c: int, num_digits: int) -> list:
         carry = (digit >> (c - 1)) & 1
         out.append((1 - overflow) * (digit - carry * (1 << c)))
     return out
+
+
+# ----------------------------------------------------------------------------------------------
+# Wire format of the reference's ffi layer (ffi/ffi_serialization.hpp:12-16, .tcc:98-187):
+# big-endian, left-padded to the in-memory width, plain values; Fq2 as c1 | c0; points affine
+# X | Y with (0, 1) for infinity.
+
+def wire_coord(group: Group, c) -> bytes:
+    return b"".join(int(v).to_bytes(group.fq.nbytes, "big") for v in group.K.coeffs(c)[::-1])
+
+
+def wire_point(group: Group, P) -> bytes:
+    K = group.K
+    if P is None:
+        return wire_coord(group, K.zero()) + wire_coord(group, K.one())
+    return wire_coord(group, P[0]) + wire_coord(group, P[1])
+
+
+def wire_scalar(group: Group, s: int) -> bytes:
+    return int(s).to_bytes(group.fr.nbytes, "big")
+
+
+def sqrt_mod(a: int, p: int):
+    """Tonelli-Shanks; None if a is not a square."""
+    a %= p
+    if a == 0:
+        return 0
+    if pow(a, (p - 1) // 2, p) != 1:
+        return None
+    if p % 4 == 3:
+        return pow(a, (p + 1) // 4, p)
+    q, s = p - 1, 0
+    while q % 2 == 0:
+        q //= 2
+        s += 1
+    z = 2
+    while pow(z, (p - 1) // 2, p) != p - 1:
+        z += 1
+    m, c, t, r = s, pow(z, q, p), pow(a, q, p), pow(a, (q + 1) // 2, p)
+    while t != 1:
+        i, t2 = 0, t
+        while t2 != 1:
+            t2 = t2 * t2 % p
+            i += 1
+        b = pow(c, 1 << (m - i - 1), p)
+        m, c = i, b * b % p
+        t, r = t * c % p, r * b % p
+    return r

@@ -70,6 +70,10 @@ def lib():
             "ref_signed_digit": (C.c_long, [i32, vp, sz, sz]),
             "ref_num_signed_digits": (sz, [i32, sz]),
             "ref_pippenger_optimal_c": (sz, [sz]),
+            "ref_wire_group_write": (sz, [i32, vp, vp, sz]),
+            "ref_wire_group_read": (sz, [i32, vp, vp, vp, sz]),
+            "ref_wire_scalar_write": (sz, [i32, vp, vp, sz]),
+            "ref_wire_scalar_read": (sz, [i32, vp, vp, vp, sz]),
         }
         for name, (res, args) in sigs.items():
             f = getattr(L, name)
@@ -200,3 +204,47 @@ def num_signed_digits(fid, c) -> int:
 
 def pippenger_optimal_c(n) -> int:
     return int(lib().ref_pippenger_optimal_c(n))
+
+
+# ---- the reference's own byte format (ffi/ffi_serialization.tcc:98-187) ------------------------
+
+def wire_point_bytes(gid: int) -> int:
+    return group_words(gid) * 8 * 2 // 3
+
+
+def wire_group_write(gid, pts) -> bytes:
+    """ffi::group_element_write of every element: affine big-endian X | Y."""
+    pts = _c(pts).reshape(-1, group_words(gid))
+    out = np.zeros((pts.shape[0], wire_point_bytes(gid)), dtype=np.uint8)
+    ok = lib().ref_wire_group_write(gid, _p(pts), out.ctypes.data_as(C.c_void_p), pts.shape[0])
+    assert ok == pts.shape[0]
+    return out.tobytes()
+
+
+def wire_group_read(gid, data: bytes):
+    """ffi::group_element_read: returns (points, accepted flags)."""
+    a = np.frombuffer(data, dtype=np.uint8)
+    n = a.size // wire_point_bytes(gid)
+    out = np.zeros((n, group_words(gid)), dtype=np.uint64)
+    okv = np.zeros(n, dtype=np.uint8)
+    lib().ref_wire_group_read(gid, a.ctypes.data_as(C.c_void_p), _p(out),
+                              okv.ctypes.data_as(C.c_void_p), n)
+    return out, okv.astype(bool)
+
+
+def wire_scalar_write(gid, scalars) -> bytes:
+    s = _c(scalars).reshape(-1, scalar_words(gid))
+    out = np.zeros((s.shape[0], scalar_words(gid) * 8), dtype=np.uint8)
+    ok = lib().ref_wire_scalar_write(gid, _p(s), out.ctypes.data_as(C.c_void_p), s.shape[0])
+    assert ok == s.shape[0]
+    return out.tobytes()
+
+
+def wire_scalar_read(gid, data: bytes):
+    a = np.frombuffer(data, dtype=np.uint8)
+    n = a.size // (scalar_words(gid) * 8)
+    out = np.zeros((n, scalar_words(gid)), dtype=np.uint64)
+    okv = np.zeros(n, dtype=np.uint8)
+    lib().ref_wire_scalar_read(gid, a.ctypes.data_as(C.c_void_p), _p(out),
+                               okv.ctypes.data_as(C.c_void_p), n)
+    return out, okv.astype(bool)

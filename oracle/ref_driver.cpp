@@ -19,6 +19,7 @@
 //   batch_to_special              multiexp.tcc:949-974
 //   field_get_signed_digit        libff/algebra/fields/field_utils.tcc:167-203
 //   SHA512_rng                    libff/common/rng.tcc:26-71
+//   ffi::group_element_read/write, field_element_read/write   ffi/ffi_serialization.tcc:98-187
 #include <cstdint>
 #include <cstring>
 #include <vector>
@@ -30,6 +31,10 @@
 #include <libff/algebra/scalar_multiplication/multiexp.hpp>
 #include <libff/common/profiling.hpp>
 #include <libff/common/rng.hpp>
+
+// the reference's own byte format (header-only templates; ffi.cpp itself is not compiled)
+#include <ffi/ffi_serialization.hpp>
+#include <ffi/ffi_serialization.tcc>
 
 #ifdef _OPENMP
 #include <omp.h>
@@ -517,3 +522,93 @@ size_t ref_num_signed_digits(int fid, size_t c)
 size_t ref_pippenger_optimal_c(size_t n) { return internal::pippenger_optimal_c(n); }
 
 } // extern "C"
+
+// ---- wire format of the reference's ffi layer (ffi/ffi_serialization.tcc:98-187) ----
+// n elements; returns the number of elements the reference's reader/writer accepted.
+template<typename G> static size_t wire_group_write(const void *in, void *out, size_t n)
+{
+    const size_t wb = 2 * sizeof(((G *)nullptr)->X);
+    size_t ok = 0;
+    for (size_t i = 0; i < n; ++i) {
+        G g;
+        std::memcpy((void *)&g, (const char *)in + i * sizeof(G), sizeof(G));
+        ok += ffi::group_element_write(g, (char *)out + i * wb, wb) ? 1 : 0;
+    }
+    return ok;
+}
+template<typename G> static size_t wire_group_read(const void *in, void *out, uint8_t *okv, size_t n)
+{
+    const size_t wb = 2 * sizeof(((G *)nullptr)->X);
+    size_t ok = 0;
+    for (size_t i = 0; i < n; ++i) {
+        G g;
+        const bool r = ffi::group_element_read(g, (const char *)in + i * wb, wb);
+        okv[i] = r;
+        ok += r ? 1 : 0;
+        std::memcpy((char *)out + i * sizeof(G), (const void *)&g, sizeof(G));
+    }
+    return ok;
+}
+template<typename F> static size_t wire_field_write(const void *in, void *out, size_t n)
+{
+    size_t ok = 0;
+    for (size_t i = 0; i < n; ++i) {
+        F f;
+        std::memcpy((void *)&f, (const char *)in + i * sizeof(F), sizeof(F));
+        ok += ffi::field_element_write(f, (char *)out + i * sizeof(F), sizeof(F)) ? 1 : 0;
+    }
+    return ok;
+}
+template<typename F> static size_t wire_field_read(const void *in, void *out, uint8_t *okv, size_t n)
+{
+    size_t ok = 0;
+    for (size_t i = 0; i < n; ++i) {
+        F f = F::zero();
+        const bool r = ffi::field_element_read(f, (const char *)in + i * sizeof(F), sizeof(F));
+        okv[i] = r;
+        ok += r ? 1 : 0;
+        std::memcpy((char *)out + i * sizeof(F), (const void *)&f, sizeof(F));
+    }
+    return ok;
+}
+
+extern "C" {
+size_t ref_wire_group_write(int gid, const void *in, void *out, size_t n)
+{
+    switch (gid) {
+    case 0: return wire_group_write<alt_bn128_G1>(in, out, n);
+    case 1: return wire_group_write<alt_bn128_G2>(in, out, n);
+    case 2: return wire_group_write<bls12_377_G1>(in, out, n);
+    case 3: return wire_group_write<bw6_761_G1>(in, out, n);
+    }
+    return 0;
+}
+size_t ref_wire_group_read(int gid, const void *in, void *out, uint8_t *okv, size_t n)
+{
+    switch (gid) {
+    case 0: return wire_group_read<alt_bn128_G1>(in, out, okv, n);
+    case 1: return wire_group_read<alt_bn128_G2>(in, out, okv, n);
+    case 2: return wire_group_read<bls12_377_G1>(in, out, okv, n);
+    case 3: return wire_group_read<bw6_761_G1>(in, out, okv, n);
+    }
+    return 0;
+}
+size_t ref_wire_scalar_write(int gid, const void *in, void *out, size_t n)
+{
+    switch (gid) {
+    case 0: case 1: return wire_field_write<alt_bn128_Fr>(in, out, n);
+    case 2: return wire_field_write<bls12_377_Fr>(in, out, n);
+    case 3: return wire_field_write<bw6_761_Fr>(in, out, n);
+    }
+    return 0;
+}
+size_t ref_wire_scalar_read(int gid, const void *in, void *out, uint8_t *okv, size_t n)
+{
+    switch (gid) {
+    case 0: case 1: return wire_field_read<alt_bn128_Fr>(in, out, okv, n);
+    case 2: return wire_field_read<bls12_377_Fr>(in, out, okv, n);
+    case 3: return wire_field_read<bw6_761_Fr>(in, out, okv, n);
+    }
+    return 0;
+}
+}

@@ -165,6 +165,18 @@ def main():
         out[f"batch_exp/{gid}/scalars"] = sc
         out[f"batch_exp/{gid}/out_raw"] = ref.batch_exp(gid, bits, window, table, sc, normalize=False)[1]
         out[f"batch_exp/{gid}/out"] = ref.batch_exp(gid, bits, window, table, sc, normalize=True)[1]
+    # ---- wire format of the reference's ffi layer (ffi/ffi_serialization.tcc:98-187)
+    for gid in range(4):
+        zero, one = ref.group_constants(gid)
+        P = ref.gen_bases_walk(gid, 3)
+        J = ref.group_op(gid, ref.G_ADD, P[:2], P[1:3])  # non-normalised: the writer normalises
+        pts = np.stack([P[0], J[0], zero, one])
+        sc = np.concatenate([pm.GROUPS[gid].encode_scalars([0, 1, pm.GROUPS[gid].fr.p - 1]),
+                             ref.gen_scalars(gid, 2, start=77)])
+        out[f"wire/{gid}/points"] = pts
+        out[f"wire/{gid}/point_bytes"] = np.frombuffer(ref.wire_group_write(gid, pts), dtype=np.uint8)
+        out[f"wire/{gid}/scalars"] = sc
+        out[f"wire/{gid}/scalar_bytes"] = np.frombuffer(ref.wire_scalar_write(gid, sc), dtype=np.uint8)
     np.savez_compressed(OUT, **out)
     print("wrote", OUT, os.path.getsize(OUT), "bytes,", len(out), "arrays")
 

@@ -311,3 +311,20 @@ def test_port_equals_live_reference(live_ref, gid):
     b = np.ascontiguousarray(J[:, w:2 * w])
     for op in (ref.OP_MUL, ref.OP_SQR, ref.OP_ADD, ref.OP_SUB, ref.OP_NEG, ref.OP_INV):
         np.testing.assert_array_equal(port.field_op(fid, op, a, b), ref.field_op(fid, op, a, b))
+
+
+# ------------------------------------------------------------------------------------------------
+# wire format of the reference's ffi layer
+
+@pytest.mark.parametrize("gid", GROUPS)
+def test_wire_format_model_matches_reference_serializer(golden, gid):
+    """ffi::group_element_write / field_element_write (ffi/ffi_serialization.tcc:98-187): big-endian
+    plain values, Fq2 as c1 | c0, affine X | Y, (0, 1) for infinity."""
+    g = pm.GROUPS[gid]
+    pts = [g.decode(r) for r in golden[f"wire/{gid}/points"]]
+    want = golden[f"wire/{gid}/point_bytes"].tobytes()
+    assert b"".join(pm.wire_point(g, P) for P in pts) == want
+    assert pts[2] is None and pm.wire_point(g, None) == want[2 * len(want) // 4:3 * len(want) // 4]
+    sc = g.decode_scalars(golden[f"wire/{gid}/scalars"])
+    assert b"".join(pm.wire_scalar(g, s) for s in sc) == golden[f"wire/{gid}/scalar_bytes"].tobytes()
+    assert len(want) // 4 == {0: 64, 1: 128, 2: 96, 3: 192}[gid]  # ffi/ffi.h:13-17,55-59 sizes
