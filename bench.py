@@ -36,6 +36,10 @@ MUL_MACS = {0: 136, 1: 136, 2: 300, 3: 1176}      # 2 N^2 + N limb-MACs per Fq m
 MIN_BYTES = {0: 96, 1: 160, 2: 128, 3: 240}       # one pass over affine bases + scalars
 
 
+# ncu --set full, k_accum_first, per launch: 28.14 GB read + 1.26 GB written
+NCU_TRAFFIC = {("alt_bn128_g1", 1 << 24): 29.40e9}
+
+
 def ceil_log2(n):
     r = 1 if n & (n - 1) else 0
     while n > 1:
@@ -287,7 +291,11 @@ def main():
         "algorithmic_unit": f"{macs} limb-MACs/point (W_ref={w_ref} x A={ADD_COST[gid]} x "
                             f"L={MUL_MACS[gid]}, c_ref={c_ref}) x 2 IMAD slots",
         "kernel_ms": accum_ms, "kernel_share_of_step": accum_ms / phase_ms["total"],
-        "traffic": None,
+        # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the committed
+        # `ncu --set full` capture of this workload (profiles/accum_first_r01b_raw.csv)
+        "traffic": NCU_TRAFFIC.get((args.group, n)),
+        "traffic_unit": "bytes per launch (ncu dram read + write); algorithmic gather = items x "
+                        "(affine point + 4-byte item)",
         "hbm_stream": {"achieved_GBps": n * MIN_BYTES[gid] / (phase_ms["total"] * 1e-3) / 1e9,
                        "peak_GBps": hbm_peak, "note": "secondary counter; the path is not HBM-bound"},
         "mont_mul_Gmul_per_s": {k: v for k, v in micro.items() if k.startswith("mont")},

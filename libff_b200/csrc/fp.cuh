@@ -22,6 +22,7 @@
 #pragma once
 #include <cstdint>
 #include "field_params.cuh"
+#include "fp_dfma.cuh"
 
 namespace b200msm {
 
@@ -221,6 +222,14 @@ struct Fp {
         return reduce_once(t);
     }
     B200_DEV static Fp sqr(const Fp &a) { return mul(a, a); }
+
+    // The same product on the FP64 pipe (fp_dfma.cuh): identical canonical result, different
+    // execution unit -- call sites split their independent products between mul and mul_d.
+    B200_DEV static Fp mul_d(const Fp &a, const Fp &b) {
+        Fp t;
+        FpDfma<P>::mul_words(t.v, a.v, b.v);
+        return reduce_once(t);
+    }
 
     // Montgomery -> plain integer (fp.tcc:270-281): one reduction of (a, 0, ..., 0)
     B200_DEV static Fp from_mont(const Fp &a) {

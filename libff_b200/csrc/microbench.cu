@@ -8,6 +8,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdio>
+#include <cstring>
 #include <cstdlib>
 
 #include "fp.cuh"
@@ -100,6 +101,37 @@ __global__ void k_dfma_imad(double *out, double seed, int iters) {
     out[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
 
+// DFMA with three distinct register operands per chain (the shape of the products in
+// fp_dfma.cuh), alone and interleaved 1:1 with IMAD.WIDE: does the FP64 pipe run beside the
+// 64-bit integer multiply-adds of fp.cuh?
+template <bool WIDE, bool FP>
+__global__ void k_dfma3_wide(double *out, double seed, int iters) {
+    double a[ILP], b[ILP], c[ILP];
+    uint64_t w[ILP];
+    uint32_t m = (uint32_t)seed | 1u;
+#pragma unroll
+    for (int i = 0; i < ILP; i++) {
+        a[i] = seed + i + threadIdx.x, b[i] = 1.0 + 1e-9 * (i + threadIdx.x), c[i] = 1e-7 * i;
+        w[i] = i + threadIdx.x;
+    }
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int u = 0; u < 8; u++)
+#pragma unroll
+            for (int i = 0; i < ILP; i++) {
+                if (FP) asm volatile("fma.rz.f64 %0, %1, %2, %0;" : "+d"(a[i]) : "d"(b[i]), "d"(c[(i + u) % ILP]));
+                if (WIDE)
+                    asm volatile("{ .reg .u32 lo; cvt.u32.u64 lo, %0; mad.wide.u32 %0, lo, %1, %0; }"
+                                 : "+l"(w[i])
+                                 : "r"(m));
+            }
+    }
+    double s = 0;
+#pragma unroll
+    for (int i = 0; i < ILP; i++) s += a[i] + (double)w[i];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
 // Random gather of 64-byte records (two uint4 per record), the access pattern of the bucket
 // accumulation; idx = hash of the record number.  Reports useful GB/s.
 __global__ void k_gather64(const uint4 *__restrict__ src, uint4 *__restrict__ dst, uint32_t mask,
@@ -135,6 +167,35 @@ __global__ void k_mont(uint32_t *out, uint32_t seed, int iters) {
     uint32_t s = 0;
 #pragma unroll
     for (int i = 0; i < P::N; i++) s ^= a.v[i] ^ b.v[i];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+// NI integer-pipe products and ND FP64-pipe products (fp_dfma.cuh) per iteration on independent
+// chains: do the two multipliers of the SM add up?
+template <class P, int NI, int ND>
+__global__ void k_mont_mix(uint32_t *out, uint32_t seed, int iters) {
+    using F = Fp<P>;
+    F x[NI + ND], b = F::one();
+    b.v[1] ^= seed * 3 + blockIdx.x;
+    b.v[P::N - 1] &= 0x0fffffff;
+#pragma unroll
+    for (int k = 0; k < NI + ND; k++) {
+        x[k] = F::one();
+        x[k].v[0] ^= seed + threadIdx.x + k;
+        x[k].v[P::N - 1] &= 0x0fffffff;
+    }
+#pragma unroll 1
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int k = 0; k < NI; k++) x[k] = F::mul_inline(x[k], b);
+#pragma unroll
+        for (int k = 0; k < ND; k++) x[NI + k] = F::mul_d(x[NI + k], b);
+    }
+    uint32_t s = 0;
+#pragma unroll
+    for (int k = 0; k < NI + ND; k++)
+#pragma unroll
+        for (int i = 0; i < P::N; i++) s ^= x[k].v[i];
     out[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
 
@@ -190,6 +251,50 @@ int main(int argc, char **argv) {
             ms = time_ms([&] { k_mont<Bw6761FqParams><<<blocks, 128>>>((uint32_t *)out, 7, iters / 8); });
             printf(", \"mont24_w%d_Gmul\": %.2f", wps, muls / 8 / ms * 1e-6);
         }
+    }
+    if (argc > 2 && !strcmp(argv[2], "prof")) {  // one launch per mix, for ncu
+#define PROF(P, NI, ND) k_mont_mix<P, NI, ND><<<sms * 4, 128>>>((uint32_t *)out, 7, iters);
+        PROF(AltBn128FqParams, 2, 0)
+        PROF(AltBn128FqParams, 0, 2)
+        PROF(AltBn128FqParams, 1, 1)
+        PROF(AltBn128FqParams, 2, 1)
+        CK(cudaDeviceSynchronize());
+        return 0;
+    }
+    if (argc > 2) {
+        for (int warps : {8, 16, 32}) {
+            int threads = warps * 32 > 1024 ? 1024 : warps * 32;
+            int blocks = sms * (warps * 32 / threads);
+            double ops = (double)blocks * threads * iters * 8.0 * ILP;
+            float ms = time_ms([&] { k_dfma3_wide<false, true><<<blocks, threads>>>((double *)out, 1.0000001, iters); });
+            printf(", \"dfma3_w%d_Tops\": %.3f", warps, ops / ms * 1e-9);
+            ms = time_ms([&] { k_dfma3_wide<true, false><<<blocks, threads>>>((double *)out, 1.0000001, iters); });
+            printf(", \"wide_w%d_Tops\": %.3f", warps, ops / ms * 1e-9);
+            ms = time_ms([&] { k_dfma3_wide<true, true><<<blocks, threads>>>((double *)out, 1.0000001, iters); });
+            printf(", \"dfma3_plus_wide_w%d_Tpairs\": %.3f", warps, ops / ms * 1e-9);
+        }
+    }
+    if (argc > 2) {  // FP64-pipe products and integer/FP64 mixes (products/s, all chains counted)
+#define MIX(P, NI, ND, tag, div)                                                                   \
+    for (int wps : {12, 16, 24, 32}) {                                                             \
+        int blocks = sms * wps / 4;                                                                \
+        int it = iters / div;                                                                      \
+        double muls = (double)blocks * 128 * it * (NI + ND);                                       \
+        float ms = time_ms([&] { k_mont_mix<P, NI, ND><<<blocks, 128>>>((uint32_t *)out, 7, it); }); \
+        printf(", \"" tag "_i%dd%d_w%d_Gmul\": %.2f", NI, ND, wps, muls / ms * 1e-6);              \
+    }
+        MIX(AltBn128FqParams, 2, 0, "mont8", 1)
+        MIX(AltBn128FqParams, 0, 2, "mont8", 1)
+        MIX(AltBn128FqParams, 1, 1, "mont8", 1)
+        MIX(AltBn128FqParams, 2, 1, "mont8", 1)
+        MIX(AltBn128FqParams, 3, 2, "mont8", 1)
+        MIX(AltBn128FqParams, 2, 2, "mont8", 1)
+        MIX(Bls12377FqParams, 2, 0, "mont12", 2)
+        MIX(Bls12377FqParams, 0, 2, "mont12", 2)
+        MIX(Bls12377FqParams, 1, 1, "mont12", 2)
+        MIX(Bls12377FqParams, 2, 1, "mont12", 2)
+        printf("}\n");
+        return 0;
     }
     {
         const uint32_t recs = 1u << 24, count = 1u << 26;  // 1 GiB of 64-byte records

@@ -47,6 +47,43 @@ def test_coordinate_field_ops(engine, ref, gid):
 
 
 @pytest.mark.parametrize("gid", GROUPS)
+def test_fp64_pipe_product_equals_reference(engine, ref, gid):
+    """Fp::mul_d (the DFMA Montgomery product, fp_dfma.cuh) is the same function as mul_reduce
+    (fp.tcc:50-228): canonical output, bit for bit, incl. 0, 1, p-1 operands."""
+    fid = ref.FQ_OF_GROUP[gid]
+    n = 4099
+    a = rand_field(ref, fid, n, 11)
+    b = rand_field(ref, fid, n, 12)
+    a[0] = 0
+    b[1] = 0
+    b[2] = a[2]
+    minus_one = ref.field_op(fid, ref.OP_NEG, _one(ref, fid))
+    a[6], b[6], a[7] = minus_one[0], minus_one[0], minus_one[0]
+    b[8] = _one(ref, fid)[0]
+    np.testing.assert_array_equal(engine.debug_op(gid, engine.FQ_MUL_D, a, b),
+                                  ref.field_op(fid, ref.OP_MUL, a, b))
+    frid = ref.FR_OF_GROUP[gid]
+    s = rand_field(ref, frid, n, 13)
+    t = rand_field(ref, frid, n, 14)
+    np.testing.assert_array_equal(engine.debug_op(gid, engine.FR_MUL_D, s, t),
+                                  ref.field_op(frid, ref.OP_MUL, s, t))
+
+
+def _one(ref, fid):
+    """Montgomery one of field fid as a (1, words) array (Fq2: (1, 0))."""
+    words = ref.lib().ref_field_bytes(fid) // 8
+    if fid == ref.F_ALT_BN128_FQ2:
+        half = words // 2
+        plain = np.zeros((1, half), dtype=np.uint64)
+        plain[0, 0] = 1
+        one = ref.field_op(ref.F_ALT_BN128_FQ, ref.OP_FROM_PLAIN, plain)
+        return np.concatenate([one, np.zeros_like(one)], axis=1)
+    plain = np.zeros((1, words), dtype=np.uint64)
+    plain[0, 0] = 1
+    return ref.field_op(fid, ref.OP_FROM_PLAIN, plain)
+
+
+@pytest.mark.parametrize("gid", GROUPS)
 def test_scalar_field_as_bigint(engine, ref, gid):
     g = pm.GROUPS[gid]
     fid = ref.FR_OF_GROUP[gid]
