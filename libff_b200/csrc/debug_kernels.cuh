@@ -20,6 +20,7 @@ enum DebugOp {
     DBG_G_DBL = 11,
     DBG_G_MADD = 12,   // b must be special (Z = 1) or zero
     DBG_G_NEG = 13,
+    DBG_FQ_MUL2 = 14,  // a b + (a + b)(a - b) through the shared-reduction product
 };
 
 template <class C>
@@ -31,14 +32,15 @@ __global__ void k_debug_op(int op, const uint32_t *__restrict__ a, const uint32_
     using X = XYZZ<F>;
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    if (op <= DBG_FQ_INV || op == DBG_FQ_MUL_D) {
+    if (op <= DBG_FQ_INV || op == DBG_FQ_MUL_D || op == DBG_FQ_MUL2) {
         F x = F::load(a + (size_t)i * F::N), y = F::zero(), r;
-        if (op <= DBG_FQ_MUL || op == DBG_FQ_MUL_D) y = F::load(b + (size_t)i * F::N);
+        if (op <= DBG_FQ_MUL || op == DBG_FQ_MUL_D || op == DBG_FQ_MUL2) y = F::load(b + (size_t)i * F::N);
         switch (op) {
             case DBG_FQ_ADD: r = F::add(x, y); break;
             case DBG_FQ_SUB: r = F::sub(x, y); break;
             case DBG_FQ_MUL: r = F::mul(x, y); break;
             case DBG_FQ_MUL_D: r = F::mul_d(x, y); break;
+            case DBG_FQ_MUL2: r = F::mul2(x, y, F::add(x, y), F::sub(x, y)); break;
             case DBG_FQ_SQR: r = F::sqr(x); break;
             case DBG_FQ_NEG: r = F::neg(x); break;
             default: r = F::inv(x); break;

@@ -67,6 +67,44 @@ B200_DEV void row_acc_shift(uint32_t *acc, const uint32_t *a, uint32_t bi) {
     asm volatile("madc.hi.u32 %0, %1, %2, 0;" : "=r"(acc[N - 1]) : "r"(a[N - 2]), "r"(bi));
 }
 
+// row_acc restricted to the even columns j >= J0 (J0 even, J0 < N): the rows of a squaring only
+// reach the columns at or above their own index
+template <int N, int J0>
+B200_DEV void row_acc_from(uint32_t *acc, const uint32_t *a, uint32_t bi) {
+    asm volatile("mad.lo.cc.u32 %0, %1, %2, %0;" : "+r"(acc[J0]) : "r"(a[J0]), "r"(bi));
+    asm volatile("madc.hi.cc.u32 %0, %1, %2, %0;" : "+r"(acc[J0 + 1]) : "r"(a[J0]), "r"(bi));
+#pragma unroll
+    for (int j = J0 + 2; j < N; j += 2) {
+        asm volatile("madc.lo.cc.u32 %0, %1, %2, %0;" : "+r"(acc[j]) : "r"(a[j]), "r"(bi));
+        asm volatile("madc.hi.cc.u32 %0, %1, %2, %0;" : "+r"(acc[j + 1]) : "r"(a[j]), "r"(bi));
+    }
+}
+
+// row_acc_shift whose products start at column J0: the columns below only move down two limbs
+// (with the carry-in from CC rippling through them)
+template <int N, int J0>
+B200_DEV void row_acc_shift_from(uint32_t *acc, const uint32_t *a, uint32_t bi) {
+#pragma unroll
+    for (int j = 0; j < N - 2; j += 2) {
+        if (j < J0) {
+            asm volatile("addc.cc.u32 %0, %1, 0;" : "=r"(acc[j]) : "r"(acc[j + 2]));
+            asm volatile("addc.cc.u32 %0, %1, 0;" : "=r"(acc[j + 1]) : "r"(acc[j + 3]));
+        } else {
+            asm volatile("madc.lo.cc.u32 %0, %1, %2, %3;" : "=r"(acc[j]) : "r"(a[j]), "r"(bi), "r"(acc[j + 2]));
+            asm volatile("madc.hi.cc.u32 %0, %1, %2, %3;"
+                : "=r"(acc[j + 1])
+                : "r"(a[j]), "r"(bi), "r"(acc[j + 3]));
+        }
+    }
+    if (N - 2 < J0) {
+        asm volatile("addc.cc.u32 %0, 0, 0;" : "=r"(acc[N - 2]));
+        asm volatile("addc.u32 %0, 0, 0;" : "=r"(acc[N - 1]));
+    } else {
+        asm volatile("madc.lo.cc.u32 %0, %1, %2, 0;" : "=r"(acc[N - 2]) : "r"(a[N - 2]), "r"(bi));
+        asm volatile("madc.hi.u32 %0, %1, %2, 0;" : "=r"(acc[N - 1]) : "r"(a[N - 2]), "r"(bi));
+    }
+}
+
 }  // namespace limb
 
 template <class P>
@@ -172,13 +210,23 @@ struct Fp {
         return r;
     }
 
-    // One row of the Montgomery product: T += a*bi; m = T[0]*INV; T += m*p; T >>= 32, with
-    // T = E + (O << 32).  On return the roles of E and O are swapped for the caller.
-    B200_DEV static void mont_row(uint32_t *E, uint32_t *O, const uint32_t *a, uint32_t bi,
-                                  bool first) {
+    // Second half of every row: m = T[0]*INV; T += m*p; T >>= 32, with T = E + (O << 32).  On
+    // return the roles of E and O are swapped for the caller.
+    B200_DEV static void reduce_row(uint32_t *E, uint32_t *O) {
         uint32_t mod[N];
 #pragma unroll
         for (int i = 0; i < N; i++) mod[i] = P::mod(i);
+        uint32_t m = E[0] * P::INV;
+        limb::row_acc<N>(O, mod + 1, m);
+        // O never carries out of N limbs (T < 2^(32(N+1))); this keeps the flag dead
+        asm volatile("addc.u32 %0, %0, 0;" : "+r"(O[N - 1]));
+        limb::row_acc<N>(E, mod, m);
+        asm volatile("addc.u32 %0, %0, 0;" : "+r"(O[N - 1]));
+    }
+
+    // One row of the Montgomery product: T += a*bi, then reduce_row.
+    B200_DEV static void mont_row(uint32_t *E, uint32_t *O, const uint32_t *a, uint32_t bi,
+                                  bool first) {
         if (first) {
             limb::row_set<N>(O, a + 1, bi);
             limb::row_set<N>(E, a, bi);
@@ -188,12 +236,72 @@ struct Fp {
             limb::row_acc<N>(E, a, bi);
             asm volatile("addc.u32 %0, %0, 0;" : "+r"(O[N - 1]));
         }
-        uint32_t m = E[0] * P::INV;
-        limb::row_acc<N>(O, mod + 1, m);
-        // O never carries out of N limbs (T < 2^(32(N+1))); this keeps the flag dead
+        reduce_row(E, O);
+    }
+
+    // One row of a sum of two products: T += a*bi + c*di, then reduce_row.  One reduction serves
+    // both products; a*b + c*d < 2 p^2 < p R / 2 keeps the result below 2p.
+    B200_DEV static void mont_row2(uint32_t *E, uint32_t *O, const uint32_t *a, uint32_t bi,
+                                   const uint32_t *c, uint32_t di, bool first) {
+        if (first) {
+            limb::row_set<N>(O, a + 1, bi);
+            limb::row_set<N>(E, a, bi);
+        } else {
+            asm volatile("add.cc.u32 %0, %0, %1;" : "+r"(E[0]) : "r"(O[1]));
+            limb::row_acc_shift<N>(O, a + 1, bi);
+            limb::row_acc<N>(E, a, bi);
+            asm volatile("addc.u32 %0, %0, 0;" : "+r"(O[N - 1]));
+        }
+        limb::row_acc<N>(O, c + 1, di);
+        asm volatile("addc.u32 %0, %0, 0;" : "+r"(O[N - 1]));  // dead flag, as in reduce_row
+        limb::row_acc<N>(E, c, di);
         asm volatile("addc.u32 %0, %0, 0;" : "+r"(O[N - 1]));
-        limb::row_acc<N>(E, mod, m);
-        asm volatile("addc.u32 %0, %0, 0;" : "+r"(O[N - 1]));
+        reduce_row(E, O);
+    }
+
+    // Row I of a squaring.  a^2 = sum_I 2^(32 I) a_I w_I with w_I = a_I 2^(32 I) + sum_{j>I}
+    // 2 a_j 2^(32 j): limb I of w_I is a_I, limb I+1 is limb I+1 of 2a without its lowest bit
+    // (that bit is the top bit of a_I), the limbs above are those of 2a.  Row I therefore only
+    // reaches columns >= I: N (N + 1) / 2 products instead of N^2 (fp.tcc:632-677 is the
+    // reference's squaring; only its 3-limb asm path is specialised there).
+    template <int I>
+    B200_DEV static void sqr_row(uint32_t *E, uint32_t *O, const uint32_t *a, const uint32_t *a2) {
+        uint32_t w[N];
+#pragma unroll
+        for (int j = 0; j < N; j++) w[j] = a2[j];
+        w[I] = a[I];
+        if constexpr (I + 1 < N) w[I + 1] = a2[I + 1] & ~1u;
+        constexpr int J0E = (I % 2 == 0) ? I : I + 1;  // even columns >= I
+        constexpr int J0O = (I % 2 == 1) ? I - 1 : I;  // odd columns >= I, as indices into w + 1
+        if constexpr (I == 0) {
+            limb::row_set<N>(O, w + 1, a[0]);
+            limb::row_set<N>(E, w, a[0]);
+        } else {
+            asm volatile("add.cc.u32 %0, %0, %1;" : "+r"(E[0]) : "r"(O[1]));
+            limb::row_acc_shift_from<N, J0O>(O, w + 1, a[I]);
+            if constexpr (J0E < N) {
+                limb::row_acc_from<N, J0E>(E, w, a[I]);
+                asm volatile("addc.u32 %0, %0, 0;" : "+r"(O[N - 1]));
+            }
+        }
+        reduce_row(E, O);
+    }
+    template <int I>
+    B200_DEV static void sqr_rows(uint32_t *E, uint32_t *O, const uint32_t *a, const uint32_t *a2) {
+        if constexpr (I < N) {
+            sqr_row<I>(E, O, a, a2);
+            sqr_rows<I + 1>(O, E, a, a2);  // the accumulators swap roles every row
+        }
+    }
+    // T = E + (O << 32) after the last row -> canonical element
+    B200_DEV static Fp finish(const uint32_t *E, const uint32_t *O) {
+        Fp t;
+        asm volatile("add.cc.u32 %0, %1, %2;" : "=r"(t.v[0]) : "r"(E[0]), "r"(O[1]));
+#pragma unroll
+        for (int i = 1; i < N - 1; i++)
+            asm volatile("addc.cc.u32 %0, %1, %2;" : "=r"(t.v[i]) : "r"(E[i]), "r"(O[i + 1]));
+        asm volatile("addc.u32 %0, %1, 0;" : "=r"(t.v[N - 1]) : "r"(E[N - 1]));
+        return reduce_once(t);
     }
 
     // fp.tcc:50-228: a*b*R^-1 mod p, canonical.  Wide fields call one shared copy of the
@@ -213,15 +321,48 @@ struct Fp {
             mont_row(E, O, a.v, b.v[i], i == 0);
             mont_row(O, E, a.v, b.v[i + 1], false);
         }
-        Fp t;
-        asm volatile("add.cc.u32 %0, %1, %2;" : "=r"(t.v[0]) : "r"(E[0]), "r"(O[1]));
-#pragma unroll
-        for (int i = 1; i < N - 1; i++)
-            asm volatile("addc.cc.u32 %0, %1, %2;" : "=r"(t.v[i]) : "r"(E[i]), "r"(O[i + 1]));
-        asm volatile("addc.u32 %0, %1, 0;" : "=r"(t.v[N - 1]) : "r"(E[N - 1]));
-        return reduce_once(t);
+        return finish(E, O);
     }
-    B200_DEV static Fp sqr(const Fp &a) { return mul(a, a); }
+
+    // fp.tcc:632-677: a*a*R^-1 mod p with N (N + 1) / 2 + N^2 limb products instead of 2 N^2
+    B200_DEV static Fp sqr(const Fp &a) {
+        if constexpr (N >= 24)
+            return sqr_call(a);
+        else
+            return sqr_inline(a);
+    }
+    __device__ __noinline__ static Fp sqr_call(const Fp &a) { return sqr_inline(a); }
+    B200_DEV static Fp sqr_inline(const Fp &a) {
+        uint32_t a2[N];  // 2a fits: the top limb has spare bits
+        asm volatile("add.cc.u32 %0, %1, %1;" : "=r"(a2[0]) : "r"(a.v[0]));
+#pragma unroll
+        for (int i = 1; i < N - 1; i++) asm volatile("addc.cc.u32 %0, %1, %1;" : "=r"(a2[i]) : "r"(a.v[i]));
+        asm volatile("addc.u32 %0, %1, %1;" : "=r"(a2[N - 1]) : "r"(a.v[N - 1]));
+        uint32_t E[N], O[N];
+        sqr_rows<0>(E, O, a.v, a2);
+        return finish(E, O);
+    }
+
+    // (a*b + c*d)*R^-1 mod p, canonical, with ONE reduction: 3 N^2 limb products instead of
+    // 4 N^2.  The group law's Y3 = R (Q - X3) - Y1 PPP is such a sum (with -Y1).
+    B200_DEV static Fp mul2(const Fp &a, const Fp &b, const Fp &c, const Fp &d) {
+        if constexpr (N >= 24)
+            return mul2_call(a, b, c, d);
+        else
+            return mul2_inline(a, b, c, d);
+    }
+    __device__ __noinline__ static Fp mul2_call(const Fp &a, const Fp &b, const Fp &c, const Fp &d) {
+        return mul2_inline(a, b, c, d);
+    }
+    B200_DEV static Fp mul2_inline(const Fp &a, const Fp &b, const Fp &c, const Fp &d) {
+        uint32_t E[N], O[N];
+#pragma unroll
+        for (int i = 0; i < N; i += 2) {
+            mont_row2(E, O, a.v, b.v[i], c.v, d.v[i], i == 0);
+            mont_row2(O, E, a.v, b.v[i + 1], c.v, d.v[i + 1], false);
+        }
+        return finish(E, O);
+    }
 
     // The same product on the FP64 pipe (fp_dfma.cuh): identical canonical result, different
     // execution unit -- call sites split their independent products between mul and mul_d.

@@ -47,6 +47,10 @@ struct Fp2 {
         F s = F::mul_d(F::add(a.c0, a.c1), F::add(b.c0, b.c1));
         return Fp2{F::sub(v0, v1), F::sub(F::sub(s, v0), v1)};
     }
+    // a b + c d (no shared reduction in the extension: the base-field products already pair up)
+    B200_DEV static Fp2 mul2(const Fp2 &a, const Fp2 &b, const Fp2 &c, const Fp2 &d) {
+        return add(mul(a, b), mul(c, d));
+    }
     // (a0 + a1 u)^2 = (a0 + a1)(a0 - a1) + 2 a0 a1 u
     __device__ __noinline__ static Fp2 sqr(const Fp2 &a) {
         F t = F::mul(a.c0, a.c1);

@@ -63,7 +63,7 @@ struct XYZZ {
         F xx = F::sqr(x);
         F M = F::add(F::dbl(xx), xx);
         F X3 = F::sub(F::sqr(M), F::dbl(S));
-        F Y3 = F::sub(F::mul(M, F::sub(S, X3)), F::mul(W, y));
+        F Y3 = F::mul2(M, F::sub(S, X3), F::neg(W), y);
         return XYZZ{X3, Y3, V, W};
     }
 
@@ -76,7 +76,7 @@ struct XYZZ {
         F xx = F::sqr(p.X);
         F M = F::add(F::dbl(xx), xx);
         F X3 = F::sub(F::sqr(M), F::dbl(S));
-        F Y3 = F::sub(F::mul(M, F::sub(S, X3)), F::mul(W, p.Y));
+        F Y3 = F::mul2(M, F::sub(S, X3), F::neg(W), p.Y);
         return XYZZ{X3, Y3, F::mul(V, p.ZZ), F::mul(W, p.ZZZ)};
     }
 
@@ -99,7 +99,7 @@ struct XYZZ {
         F PPP = F::mul(Pd, PP);
         F Q = F::mul(acc.X, PP);
         F X3 = F::sub(F::sub(F::sqr(R), PPP), F::dbl(Q));
-        F Y3 = F::sub(F::mul(R, F::sub(Q, X3)), F::mul(acc.Y, PPP));
+        F Y3 = F::mul2(R, F::sub(Q, X3), F::neg(acc.Y), PPP);  // one reduction for both products
         acc.X = X3;
         acc.Y = Y3;
         acc.ZZ = F::mul(acc.ZZ, PP);
@@ -128,7 +128,7 @@ struct XYZZ {
         F PPP = F::mul(Pd, PP);
         F Q = F::mul(U1, PP);
         F X3 = F::sub(F::sub(F::sqr(R), PPP), F::dbl(Q));
-        F Y3 = F::sub(F::mul(R, F::sub(Q, X3)), F::mul(S1, PPP));
+        F Y3 = F::mul2(R, F::sub(Q, X3), F::neg(S1), PPP);
         acc.X = X3;
         acc.Y = Y3;
         acc.ZZ = F::mul(F::mul(acc.ZZ, q.ZZ), PP);

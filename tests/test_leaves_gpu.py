@@ -69,6 +69,29 @@ def test_fp64_pipe_product_equals_reference(engine, ref, gid):
                                   ref.field_op(frid, ref.OP_MUL, s, t))
 
 
+@pytest.mark.parametrize("gid", GROUPS)
+def test_shared_reduction_product_and_squaring(engine, ref, gid):
+    """Fp::mul2 (a b + c d with one Montgomery reduction) and the dedicated Fp::sqr against the
+    reference's field operations (fp.tcc:50-228, 632-677), incl. 0, 1 and p-1 operands."""
+    fid = ref.FQ_OF_GROUP[gid]
+    n = 4099
+    a = rand_field(ref, fid, n, 21)
+    b = rand_field(ref, fid, n, 22)
+    minus_one = ref.field_op(fid, ref.OP_NEG, _one(ref, fid))
+    a[0] = 0
+    b[1] = 0
+    b[2] = a[2]
+    a[3], b[3] = minus_one[0], minus_one[0]
+    a[4], b[4] = minus_one[0], _one(ref, fid)[0]
+    a[5] = _one(ref, fid)[0]
+    want = ref.field_op(fid, ref.OP_ADD, ref.field_op(fid, ref.OP_MUL, a, b),
+                        ref.field_op(fid, ref.OP_MUL, ref.field_op(fid, ref.OP_ADD, a, b),
+                                     ref.field_op(fid, ref.OP_SUB, a, b)))
+    np.testing.assert_array_equal(engine.debug_op(gid, engine.FQ_MUL2, a, b), want)
+    np.testing.assert_array_equal(engine.debug_op(gid, engine.FQ_SQR, a),
+                                  ref.field_op(fid, ref.OP_SQR, a))
+
+
 def _one(ref, fid):
     """Montgomery one of field fid as a (1, words) array (Fq2: (1, 0))."""
     words = ref.lib().ref_field_bytes(fid) // 8
