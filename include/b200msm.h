@@ -45,7 +45,12 @@ extern "C" {
 #define B200MSM_ALT_BN128_G2 1u /* 192 B elements, 32 B scalars */
 #define B200MSM_BLS12_377_G1 2u /* 144 B elements, 32 B scalars */
 #define B200MSM_BW6_761_G1 3u   /* 288 B elements, 48 B scalars */
-#define B200MSM_NUM_GROUPS 4u
+/* the remaining groups of the same curve families */
+#define B200MSM_BLS12_377_G2 4u /* 288 B elements (Fq2 coordinates), 32 B scalars */
+#define B200MSM_BW6_761_G2 5u   /* 288 B elements, 48 B scalars */
+#define B200MSM_BLS12_381_G1 6u /* 144 B elements, 32 B scalars */
+#define B200MSM_BLS12_381_G2 7u /* 288 B elements (Fq2 coordinates), 32 B scalars */
+#define B200MSM_NUM_GROUPS 8u
 
 /* multi_exp_base_form (multiexp.hpp:49-58) */
 #define B200MSM_FORM_NORMAL 0u  /* arbitrary Z */

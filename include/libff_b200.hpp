@@ -3,7 +3,7 @@
  * Include this header immediately after
  *     #include <libff/algebra/scalar_multiplication/multiexp.hpp>
  * (and the curve headers) and before any call site, then link libb200msm.so.  It provides explicit
- * (full) specialisations of the reference templates for the four groups of the path:
+ * (full) specialisations of the reference templates for the groups of the path:
  *
  *   libff::multi_exp<G, Fr, multi_exp_method_BDLO12 | _BDLO12_signed, normal | special>
  *                                                   multiexp.hpp:63-73, multiexp.tcc:643-688
@@ -14,7 +14,9 @@
  *                                                   multiexp.hpp:120-134, multiexp.tcc:875-915
  *   libff::batch_to_special<G>(vec)                 multiexp.hpp:144, multiexp.tcc:949-974
  *
- * for G in { alt_bn128_G1, alt_bn128_G2, bls12_377_G1, bw6_761_G1 } with their scalar fields.
+ * for G in { alt_bn128_G1, alt_bn128_G2, bls12_377_G1, bw6_761_G1 } (the path's four groups) and
+ * { bls12_377_G2, bw6_761_G2, bls12_381_G1, bls12_381_G2 } (bls12_381 is in the
+ * reference's own multiexp tests, test_multiexp.cpp:322-326) with their scalar fields.
  * Call sites stay source-identical (libff's own test, test_multiexp.cpp, compiles unchanged: see
  * tests/cpp/dropin_test.cpp).  Everything forwards to the C ABI of include/b200msm.h with
  * `&*vec.begin()`: no conversion, libff's in-memory layout is the wire format.
@@ -36,6 +38,7 @@
 #include <cstdlib>
 #include <libff/algebra/curves/alt_bn128/alt_bn128_pp.hpp>
 #include <libff/algebra/curves/bls12_377/bls12_377_pp.hpp>
+#include <libff/algebra/curves/bls12_381/bls12_381_pp.hpp>
 #include <libff/algebra/curves/bw6_761/bw6_761_pp.hpp>
 #include <libff/algebra/scalar_multiplication/multiexp.hpp>
 #include <mutex>
@@ -62,6 +65,18 @@ template<> struct group_id<bls12_377_G1> {
 };
 template<> struct group_id<bw6_761_G1> {
     static constexpr uint32_t value = B200MSM_BW6_761_G1;
+};
+template<> struct group_id<bls12_377_G2> {
+    static constexpr uint32_t value = B200MSM_BLS12_377_G2;
+};
+template<> struct group_id<bw6_761_G2> {
+    static constexpr uint32_t value = B200MSM_BW6_761_G2;
+};
+template<> struct group_id<bls12_381_G1> {
+    static constexpr uint32_t value = B200MSM_BLS12_381_G1;
+};
+template<> struct group_id<bls12_381_G2> {
+    static constexpr uint32_t value = B200MSM_BLS12_381_G2;
 };
 
 [[noreturn]] inline void fail(const char *what)
@@ -282,6 +297,10 @@ LIBFF_B200_SPECIALISE_GROUP(alt_bn128_G1, alt_bn128_Fr)
 LIBFF_B200_SPECIALISE_GROUP(alt_bn128_G2, alt_bn128_Fr)
 LIBFF_B200_SPECIALISE_GROUP(bls12_377_G1, bls12_377_Fr)
 LIBFF_B200_SPECIALISE_GROUP(bw6_761_G1, bw6_761_Fr)
+LIBFF_B200_SPECIALISE_GROUP(bls12_377_G2, bls12_377_Fr)
+LIBFF_B200_SPECIALISE_GROUP(bw6_761_G2, bw6_761_Fr)
+LIBFF_B200_SPECIALISE_GROUP(bls12_381_G1, bls12_381_Fr)
+LIBFF_B200_SPECIALISE_GROUP(bls12_381_G2, bls12_381_Fr)
 
 #undef LIBFF_B200_SPECIALISE_GROUP
 #undef LIBFF_B200_SPECIALISE_MULTI_EXP

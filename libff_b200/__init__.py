@@ -25,7 +25,8 @@ from typing import Optional, Sequence
 import numpy as np
 
 __all__ = [
-    "ALT_BN128_G1", "ALT_BN128_G2", "BLS12_377_G1", "BW6_761_G1", "GROUP_NAMES",
+    "ALT_BN128_G1", "ALT_BN128_G2", "BLS12_377_G1", "BW6_761_G1", "BLS12_377_G2", "BW6_761_G2",
+    "BLS12_381_G1", "BLS12_381_G2", "GROUP_NAMES",
     "FORM_NORMAL", "FORM_SPECIAL", "B200MsmError", "lib_path", "load", "init", "shutdown",
     "group_bytes", "scalar_bytes", "multi_exp", "batch_exp", "batch_to_special", "group_sum",
     "ResidentBases", "ResidentScalars", "multi_exp_resident", "last_timings", "launch_count",
@@ -34,7 +35,9 @@ __all__ = [
 ]
 
 ALT_BN128_G1, ALT_BN128_G2, BLS12_377_G1, BW6_761_G1 = 0, 1, 2, 3
-GROUP_NAMES = {0: "alt_bn128_G1", 1: "alt_bn128_G2", 2: "bls12_377_G1", 3: "bw6_761_G1"}
+BLS12_377_G2, BW6_761_G2, BLS12_381_G1, BLS12_381_G2 = 4, 5, 6, 7
+GROUP_NAMES = {0: "alt_bn128_G1", 1: "alt_bn128_G2", 2: "bls12_377_G1", 3: "bw6_761_G1",
+               4: "bls12_377_G2", 5: "bw6_761_G2", 6: "bls12_381_G1", 7: "bls12_381_G2"}
 FORM_NORMAL, FORM_SPECIAL = 0, 1  # multi_exp_base_form (multiexp.hpp:49-58)
 
 # every symbol include/b200msm.h declares (tests check the library exports all of them)

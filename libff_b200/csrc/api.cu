@@ -82,6 +82,10 @@ const GroupOps *ops_for(uint32_t group) {
         case B200MSM_ALT_BN128_G2: return ops_alt_bn128_g2();
         case B200MSM_BLS12_377_G1: return ops_bls12_377_g1();
         case B200MSM_BW6_761_G1: return ops_bw6_761_g1();
+        case B200MSM_BLS12_377_G2: return ops_bls12_377_g2();
+        case B200MSM_BW6_761_G2: return ops_bw6_761_g2();
+        case B200MSM_BLS12_381_G1: return ops_bls12_381_g1();
+        case B200MSM_BLS12_381_G2: return ops_bls12_381_g2();
     }
     return nullptr;
 }

@@ -7,6 +7,11 @@
 //   alt_bn128_G2  Jacobian/Fq2, 192 B libff/algebra/curves/alt_bn128/alt_bn128_g2.hpp:45
 //   bls12_377_G1  Jacobian, 144 B     libff/algebra/curves/bls12_377/bls12_377_g1.hpp:44
 //   bw6_761_G1    homogeneous projective, 288 B   libff/algebra/curves/bw6_761/bw6_761_g1.hpp:37-39
+// and the remaining groups of the reference's pairing-friendly families:
+//   bls12_377_G2  Jacobian/Fq2, 288 B libff/algebra/curves/bls12_377/bls12_377_g2.hpp:45
+//   bw6_761_G2    homogeneous projective over Fq, 288 B  bw6_761/bw6_761_g2.hpp:39
+//   bls12_381_G1  Jacobian, 144 B     libff/algebra/curves/bls12_381/bls12_381_g1.hpp:44
+//   bls12_381_G2  Jacobian/Fq2, 288 B libff/algebra/curves/bls12_381/bls12_381_g2.hpp:45
 // Infinity: Jacobian Z = 0 (alt_bn128_g1.cpp:91); bw6_761 X = 0 and Z = 0 (bw6_761_g1.cpp:79-82).
 #pragma once
 #include "xyzz.cuh"
@@ -36,6 +41,31 @@ struct Bw6761G1 {
     using Fq = Fp<Bw6761FqParams>;
     using Fr = Fp<Bls12377FqParams>;  // bw6_761 Fr is bls12_377 Fq (bw6_761_init.cpp:35-59)
     static constexpr bool PROJECTIVE = true;
+};
+
+struct Bls12377G2 {
+    static constexpr int ID = 4;
+    using Fq = Fp2<Bls12377FqParams, 5>;  // u^2 = -5 (bls12_377_init.cpp:170-176)
+    using Fr = Fp<Bls12377FrParams>;
+    static constexpr bool PROJECTIVE = false;
+};
+struct Bw6761G2 {
+    static constexpr int ID = 5;
+    using Fq = Fp<Bw6761FqParams>;        // the M-twist is defined over Fq itself
+    using Fr = Fp<Bls12377FqParams>;
+    static constexpr bool PROJECTIVE = true;
+};
+struct Bls12381G1 {
+    static constexpr int ID = 6;
+    using Fq = Fp<Bls12381FqParams>;
+    using Fr = Fp<Bls12381FrParams>;
+    static constexpr bool PROJECTIVE = false;
+};
+struct Bls12381G2 {
+    static constexpr int ID = 7;
+    using Fq = Fp2<Bls12381FqParams, 1>;  // u^2 = -1 (bls12_381_init.cpp:137-139)
+    using Fr = Fp<Bls12381FrParams>;
+    static constexpr bool PROJECTIVE = false;
 };
 
 template <class C>

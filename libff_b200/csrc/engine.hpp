@@ -131,5 +131,9 @@ const GroupOps *ops_alt_bn128_g1();
 const GroupOps *ops_alt_bn128_g2();
 const GroupOps *ops_bls12_377_g1();
 const GroupOps *ops_bw6_761_g1();
+const GroupOps *ops_bls12_377_g2();
+const GroupOps *ops_bw6_761_g2();
+const GroupOps *ops_bls12_381_g1();
+const GroupOps *ops_bls12_381_g2();
 
 }  // namespace b200msm

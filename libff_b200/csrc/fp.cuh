@@ -111,6 +111,10 @@ template <class P>
 struct Fp {
     static constexpr int N = P::N;
     using Params = P;
+    // The squaring rows and the shared-reduction product accumulate up to 3p before the shift,
+    // which needs p < 2^(32 N - 2); every coordinate field here has the two spare bits, the
+    // 255-bit bls12_381 Fr (scalars only) has one and takes the plain product instead.
+    static constexpr bool SPARE2 = (P::mod(N - 1) >> 30) == 0;
     uint32_t v[N];
 
     B200_DEV static Fp zero() {
@@ -326,7 +330,9 @@ struct Fp {
 
     // fp.tcc:632-677: a*a*R^-1 mod p with N (N + 1) / 2 + N^2 limb products instead of 2 N^2
     B200_DEV static Fp sqr(const Fp &a) {
-        if constexpr (N >= 24)
+        if constexpr (!SPARE2)
+            return mul(a, a);
+        else if constexpr (N >= 24)
             return sqr_call(a);
         else
             return sqr_inline(a);
@@ -346,7 +352,9 @@ struct Fp {
     // (a*b + c*d)*R^-1 mod p, canonical, with ONE reduction: 3 N^2 limb products instead of
     // 4 N^2.  The group law's Y3 = R (Q - X3) - Y1 PPP is such a sum (with -Y1).
     B200_DEV static Fp mul2(const Fp &a, const Fp &b, const Fp &c, const Fp &d) {
-        if constexpr (N >= 24)
+        if constexpr (!SPARE2)
+            return add(mul(a, b), mul(c, d));
+        else if constexpr (N >= 24)
             return mul2_call(a, b, c, d);
         else
             return mul2_inline(a, b, c, d);

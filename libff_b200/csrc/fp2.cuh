@@ -1,16 +1,18 @@
-// Quadratic extension Fq2 = Fq[u]/(u^2 + 1) for alt_bn128 G2 coordinates.
+// Quadratic extension Fq2 = Fq[u]/(u^2 + NR) for G2 coordinates, NR a small positive integer:
+// alt_bn128 and bls12_381 u^2 = -1 (alt_bn128_init.cpp:138-140, bls12_381_init.cpp:137-139),
+// bls12_377 u^2 = -5 (bls12_377_init.cpp:170-176).
 //
 // Replaces Fp2_model (libff/algebra/fields/fp2.tcc): mul :101-114 (Karatsuba), squared_complex
 // :141-151, inverse :153-168, add/sub/neg :79-120.  The reference multiplies by `non_residue`
-// with a full Fq multiplication; for alt_bn128 non_residue = q - 1 = -1
-// (alt_bn128_init.cpp:138-140), so here it is a subtraction -- same value, canonical result.
+// with a full Fq multiplication; here -NR x is a few additions and a subtraction -- same value,
+// canonical result.
 // Memory layout = the reference's: c0 limbs then c1 limbs (fp2.hpp `Fp_model coeffs[2]`).
 #pragma once
 #include "fp.cuh"
 
 namespace b200msm {
 
-template <class P>
+template <class P, int NR = 1>
 struct Fp2 {
     using F = Fp<P>;
     static constexpr int N = 2 * P::N;  // 32-bit words per element
@@ -33,33 +35,43 @@ struct Fp2 {
     B200_DEV static Fp2 select(bool f, const Fp2 &a, const Fp2 &b) {
         return Fp2{F::select(f, a.c0, b.c0), F::select(f, a.c1, b.c1)};
     }
-    // (a0 + a1 u)(b0 + b1 u) = (a0 b0 - a1 b1) + ((a0 + a1)(b0 + b1) - a0 b0 - a1 b1) u
+    // NR * x by additions (NR is 1 or 5)
+    B200_DEV static F times_nr(const F &x) {
+        if constexpr (NR == 1) {
+            return x;
+        } else {
+            static_assert(NR == 5, "non-residue -1 or -5");
+            return F::add(F::dbl(F::dbl(x)), x);
+        }
+    }
+    // (a0 + a1 u)(b0 + b1 u) = (a0 b0 - NR a1 b1) + ((a0 + a1)(b0 + b1) - a0 b0 - a1 b1) u
     __device__ __noinline__ static Fp2 mul(const Fp2 &a, const Fp2 &b) {
         F v0 = F::mul(a.c0, b.c0);
         F v1 = F::mul(a.c1, b.c1);
         F s = F::mul(F::add(a.c0, a.c1), F::add(b.c0, b.c1));
-        return Fp2{F::sub(v0, v1), F::sub(F::sub(s, v0), v1)};
+        return Fp2{F::sub(v0, times_nr(v1)), F::sub(F::sub(s, v0), v1)};
     }
     // the same with the three base-field products on the FP64 pipe (fp_dfma.cuh)
     __device__ __noinline__ static Fp2 mul_d(const Fp2 &a, const Fp2 &b) {
         F v0 = F::mul_d(a.c0, b.c0);
         F v1 = F::mul_d(a.c1, b.c1);
         F s = F::mul_d(F::add(a.c0, a.c1), F::add(b.c0, b.c1));
-        return Fp2{F::sub(v0, v1), F::sub(F::sub(s, v0), v1)};
+        return Fp2{F::sub(v0, times_nr(v1)), F::sub(F::sub(s, v0), v1)};
     }
     // a b + c d (no shared reduction in the extension: the base-field products already pair up)
     B200_DEV static Fp2 mul2(const Fp2 &a, const Fp2 &b, const Fp2 &c, const Fp2 &d) {
         return add(mul(a, b), mul(c, d));
     }
-    // (a0 + a1 u)^2 = (a0 + a1)(a0 - a1) + 2 a0 a1 u
+    // (a0 + a1 u)^2 = (a0 + a1)(a0 - NR a1) + (NR - 1) a0 a1 + 2 a0 a1 u   (fp2.tcc:141-151)
     __device__ __noinline__ static Fp2 sqr(const Fp2 &a) {
         F t = F::mul(a.c0, a.c1);
-        F c0 = F::mul(F::add(a.c0, a.c1), F::sub(a.c0, a.c1));
+        F c0 = F::mul(F::add(a.c0, a.c1), F::sub(a.c0, times_nr(a.c1)));
+        if constexpr (NR == 5) c0 = F::add(c0, F::dbl(F::dbl(t)));
         return Fp2{c0, F::dbl(t)};
     }
-    // 1 / (a0 + a1 u) = (a0 - a1 u) / (a0^2 + a1^2)
+    // 1 / (a0 + a1 u) = (a0 - a1 u) / (a0^2 + NR a1^2)
     __device__ __noinline__ static Fp2 inv(const Fp2 &a) {
-        F d = F::inv(F::add(F::sqr(a.c0), F::sqr(a.c1)));
+        F d = F::inv(F::add(F::sqr(a.c0), times_nr(F::sqr(a.c1))));
         return Fp2{F::mul(a.c0, d), F::neg(F::mul(a.c1, d))};
     }
     B200_DEV static Fp2 load(const uint32_t *p) { return Fp2{F::load(p), F::load(p + P::N)}; }

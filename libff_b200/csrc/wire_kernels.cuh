@@ -48,6 +48,41 @@ struct CurveB<Bw6761G1> {
     B200_DEV static F get() { return F::neg(F::one()); }
 };
 
+// bls12_377 twist y^2 = x^3 + 1/u (bls12_377_init.cpp:302-304): 1/u = -(1/5) u
+template <>
+struct CurveB<Bls12377G2> {
+    using F = Bls12377G2::Fq;
+    B200_DEV static F get() {
+        constexpr uint32_t c1[12] = {0x66666685u, 0x80722666u, 0x899999a9u, 0x8df55926u,
+                                     0xd64f34cfu, 0x7fe4561au, 0xb6e4f01bu, 0xb95da6d8u,
+                                     0xfc142743u, 0x4b747cccu, 0x70f49f43u, 0x0039c3fau};
+        F r = F::zero();
+#pragma unroll
+        for (int i = 0; i < 12; i++) r.c1.v[i] = c1[i];
+        return r;
+    }
+};
+// bw6_761 twist y^2 = x^3 + 4 (bw6_761_init.cpp:272-282)
+template <>
+struct CurveB<Bw6761G2> {
+    using F = Bw6761G2::Fq;
+    B200_DEV static F get() { return F::dbl(F::dbl(F::one())); }
+};
+// bls12_381 y^2 = x^3 + 4 and its twist y^2 = x^3 + 4 (1 + u) (bls12_381_init.cpp:418-420)
+template <>
+struct CurveB<Bls12381G1> {
+    using F = Bls12381G1::Fq;
+    B200_DEV static F get() { return F::dbl(F::dbl(F::one())); }
+};
+template <>
+struct CurveB<Bls12381G2> {
+    using F = Bls12381G2::Fq;
+    B200_DEV static F get() {
+        auto four = Bls12381G1::Fq::dbl(Bls12381G1::Fq::dbl(Bls12381G1::Fq::one()));
+        return F{four, four};
+    }
+};
+
 // error bits accumulated by the decode kernels
 enum WireError : uint32_t {
     WIRE_ERR_RANGE = 1,     // a coordinate or scalar >= its modulus
@@ -98,8 +133,8 @@ B200_DEV bool wire_read_coord(const uint8_t *src, Fp<P> &out, bool &is_zero, boo
     out = Fp<P>::to_mont(plain);
     return ok;
 }
-template <class P>
-B200_DEV bool wire_read_coord(const uint8_t *src, Fp2<P> &out, bool &is_zero, bool &is_one) {
+template <class P, int NR>
+B200_DEV bool wire_read_coord(const uint8_t *src, Fp2<P, NR> &out, bool &is_zero, bool &is_one) {
     bool z0, o0, z1, o1;
     bool ok1 = wire_read_coord<P>(src, out.c1, z1, o1);               // highest order first
     bool ok0 = wire_read_coord<P>(src + 4 * P::N, out.c0, z0, o0);
@@ -111,8 +146,8 @@ template <class P>
 B200_DEV void wire_write_coord(uint8_t *dst, const Fp<P> &mont) {
     wire_write_fp<P>(dst, Fp<P>::from_mont(mont));
 }
-template <class P>
-B200_DEV void wire_write_coord(uint8_t *dst, const Fp2<P> &mont) {
+template <class P, int NR>
+B200_DEV void wire_write_coord(uint8_t *dst, const Fp2<P, NR> &mont) {
     wire_write_fp<P>(dst, Fp<P>::from_mont(mont.c1));
     wire_write_fp<P>(dst + 4 * P::N, Fp<P>::from_mont(mont.c0));
 }

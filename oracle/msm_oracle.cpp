@@ -713,11 +713,20 @@ typedef Fp<4, 3> BlsFr;   // bls12_377_init.cpp:58-82
 typedef Fp<12, 4> Bw6Fq;  // bw6_761_init.cpp:81-116
 typedef Fp<6, 5> Bw6Fr;   // bw6_761_init.cpp:35-59 (= bls12_377 Fq modulus)
 typedef Fp2<BnFq> BnFq2;
+// the remaining groups of the same families
+typedef Fp<6, 6> Bls381Fq;  // bls12_381_init.cpp:76-116
+typedef Fp<4, 7> Bls381Fr;  // bls12_381_init.cpp:36-74
+typedef Fp2<BlsFq> BlsFq2;  // u^2 = -5, bls12_377_init.cpp:170-176
+typedef Fp2<Bls381Fq> Bls381Fq2;  // u^2 = -1, bls12_381_init.cpp:137-139
 
 typedef Jac<BnFq, 0> BnG1;
 typedef Jac<BnFq2, 1> BnG2;
 typedef Jac<BlsFq, 2> BlsG1;
 typedef Proj<Bw6Fq, 3> Bw6G1;
+typedef Jac<BlsFq2, 4> BlsG2;       // bls12_377_g2.cpp (same formulas as alt_bn128_g2.cpp)
+typedef Proj<Bw6Fq, 5> Bw6G2;       // bw6_761_g2.cpp (same formulas as bw6_761_g1.cpp, over Fq)
+typedef Jac<Bls381Fq, 6> Bls381G1;  // bls12_381_g1.cpp
+typedef Jac<Bls381Fq2, 7> Bls381G2; // bls12_381_g2.cpp
 
 template <class F>
 static F fq_from_hex(const char *h) {
@@ -730,6 +739,10 @@ static BnG1 g_bn_g1;
 static BnG2 g_bn_g2;
 static BlsG1 g_bls_g1;
 static Bw6G1 g_bw6_g1;
+static BlsG2 g_bls_g2;
+static Bw6G2 g_bw6_g2;
+static Bls381G1 g_bls381_g1;
+static Bls381G2 g_bls381_g2;
 static bool g_ready = false;
 
 static void init_all() {
@@ -747,7 +760,49 @@ static void init_all() {
     setup_params(Bw6Fr::P,
                  "1ae3a4617c510eac63b05c06ca1493b1a22d9f300f5138f1ef3622fba094800170b5d44300000008"
                  "508c00000000001");
+    setup_params(Bls381Fq::P,
+                 "1a0111ea397fe69a4b1ba7b6434bacd764774b84f38512bf6730d2a0f6b0f6241eabfffeb153ffff"
+                 "b9feffffffffaaab");
+    setup_params(Bls381Fr::P, "73eda753299d7d483339d80809a1d80553bda402fffe5bfeffffffff00000001");
     BnFq2::non_residue = -BnFq::one();  // q - 1, alt_bn128_init.cpp:138-140
+    BlsFq2::non_residue = -fq_from_hex<BlsFq>("5");        // bls12_377_init.cpp:170-176
+    Bls381Fq2::non_residue = -Bls381Fq::one();             // bls12_381_init.cpp:137-139
+    // generators: bls12_377_init.cpp:392-420, bw6_761_init.cpp:340-360, bls12_381_init.cpp:441-450,
+    // 517-534 (decimal literals there; read back from the compiled reference in hexadecimal)
+    g_bls_g2 = BlsG2{
+        BlsFq2{fq_from_hex<BlsFq>("b997fef930828fe1b9e6a1707b8aa508a3dbfd7fe2246499c709226a0a6fef49"
+                                  "f85b3a375363f4f8f6ea3fbd159f8a"),
+               fq_from_hex<BlsFq>("d6ac33b84947d9845f81a57a136bfa326e915fabc8cd6a57ff133b42d00f62e4"
+                                  "e1af460228cd5184deae976fa62596")},
+        BlsFq2{fq_from_hex<BlsFq>("118dd509b2e9a13744a507d515a595dbb7e3b63df568866473790184bdf83636"
+                                  "c94df2b7a962cb2af4337f07cb7e622"),
+               fq_from_hex<BlsFq>("185067c6ca76d992f064a432bd9f9be832b0cac2d824d0518f77d39e76c3e146"
+                                  "afb825f2092218d038867d7f337a010")},
+        BlsFq2::one()};
+    g_bw6_g2 = Bw6G2{
+        fq_from_hex<Bw6Fq>("110133241d9b816c852a82e69d660f9d61053aac5a7115f4c06201013890f6d26b41c5da"
+                           "b3da268734ec3f1f09feb58c5bbcae9ac70e7c7963317a300e1b6bace6948cb3cd208d70"
+                           "0e96efbc2ad54b06410cf4fe1bf995ba830c194cd025f1c"),
+        fq_from_hex<Bw6Fq>("17c3357761369f8179eb10e4b6d2dc26b7cf9acec2181c81a78e2753ffe3160a1d86c80b"
+                           "95a59c94c97eb733293fef64f293dbd2c712b88906c170ffa823003ea96fcd504affc758"
+                           "aa2d3a3c5a02a591ec0594f9eac689eb70a16728c73b61"),
+        Bw6Fq::one()};
+    g_bls381_g1 = Bls381G1{
+        fq_from_hex<Bls381Fq>("17f1d3a73197d7942695638c4fa9ac0fc3688c4f9774b905a14e3a3f171bac586c55"
+                              "e83ff97a1aeffb3af00adb22c6bb"),
+        fq_from_hex<Bls381Fq>("8b3f481e3aaa0f1a09e30ed741d8ae4fcf5e095d5d00af600db18cb2c04b3edd03cc"
+                              "744a2888ae40caa232946c5e7e1"),
+        Bls381Fq::one()};
+    g_bls381_g2 = Bls381G2{
+        Bls381Fq2{fq_from_hex<Bls381Fq>("24aa2b2f08f0a91260805272dc51051c6e47ad4fa403b02b4510b647ae"
+                                        "3d1770bac0326a805bbefd48056c8c121bdb8"),
+                  fq_from_hex<Bls381Fq>("13e02b6052719f607dacd3a088274f65596bd0d09920b61ab5da61bbdc"
+                                        "7f5049334cf11213945d57e5ac7d055d042b7e")},
+        Bls381Fq2{fq_from_hex<Bls381Fq>("ce5d527727d6e118cc9cdc6da2e351aadfd9baa8cbdd3a76d429a6951"
+                                        "60d12c923ac9cc3baca289e193548608b82801"),
+                  fq_from_hex<Bls381Fq>("606c4a02ea734cc32acd2b02bc28b99cb3e287e85a763af267492ab57"
+                                        "2e99ab3f370d275cec1da1aaa9075ff05f79be")},
+        Bls381Fq2::one()};
     // generators: alt_bn128_init.cpp:289-290,358-369; bls12_377_init.cpp:324-331;
     // bw6_761_init.cpp:287-296 (decimal literals there, hexadecimal here)
     g_bn_g1 = BnG1{fq_from_hex<BnFq>("1"), fq_from_hex<BnFq>("2"), BnFq::one()};
@@ -779,6 +834,10 @@ template <> const BnG1 &generator<BnG1>() { return g_bn_g1; }
 template <> const BnG2 &generator<BnG2>() { return g_bn_g2; }
 template <> const BlsG1 &generator<BlsG1>() { return g_bls_g1; }
 template <> const Bw6G1 &generator<Bw6G1>() { return g_bw6_g1; }
+template <> const BlsG2 &generator<BlsG2>() { return g_bls_g2; }
+template <> const Bw6G2 &generator<Bw6G2>() { return g_bw6_g2; }
+template <> const Bls381G1 &generator<Bls381G1>() { return g_bls381_g1; }
+template <> const Bls381G2 &generator<Bls381G2>() { return g_bls381_g2; }
 
 template <class G, class Fr>
 struct Ops {
@@ -853,6 +912,10 @@ struct Ops {
         case 1: return Ops<BnG2, BnFr>::call;                   \
         case 2: return Ops<BlsG1, BlsFr>::call;                 \
         case 3: return Ops<Bw6G1, Bw6Fr>::call;                 \
+        case 4: return Ops<BlsG2, BlsFr>::call;                 \
+        case 5: return Ops<Bw6G2, Bw6Fr>::call;                 \
+        case 6: return Ops<Bls381G1, Bls381Fr>::call;           \
+        case 7: return Ops<Bls381G2, Bls381Fr>::call;           \
     }
 
 template <class F>
@@ -916,6 +979,8 @@ static size_t num_signed_digits(size_t c) {
         case 3: { using F = BlsFr; expr; } break;  \
         case 4: { using F = Bw6Fq; expr; } break;  \
         case 5: { using F = Bw6Fr; expr; } break;  \
+        case 8: { using F = Bls381Fq; expr; } break; \
+        case 9: { using F = Bls381Fr; expr; } break; \
     }
 
 // ------------------------------------------------------------------------------------------------
@@ -988,19 +1053,20 @@ void orc_set_num_threads(int t) {
 #endif
 }
 size_t orc_group_bytes(int gid) {
-    static const size_t b[4] = {96, 192, 144, 288};
-    return gid >= 0 && gid < 4 ? b[gid] : 0;
+    static const size_t b[8] = {96, 192, 144, 288, 288, 288, 144, 288};
+    return gid >= 0 && gid < 8 ? b[gid] : 0;
 }
 size_t orc_scalar_bytes(int gid) {
-    static const size_t b[4] = {32, 32, 32, 48};
-    return gid >= 0 && gid < 4 ? b[gid] : 0;
+    static const size_t b[8] = {32, 32, 32, 48, 32, 48, 32, 32};
+    return gid >= 0 && gid < 8 ? b[gid] : 0;
 }
 size_t orc_scalar_bits(int gid) {
     init_all();
     switch (gid) {
         case 0: case 1: return BnFr::P.bits;
-        case 2: return BlsFr::P.bits;
-        case 3: return Bw6Fr::P.bits;
+        case 2: case 4: return BlsFr::P.bits;
+        case 3: case 5: return Bw6Fr::P.bits;
+        case 6: case 7: return Bls381Fr::P.bits;
     }
     return 0;
 }
@@ -1019,6 +1085,10 @@ void orc_scalar_mul(int gid, const void *base, const void *scalar, void *out, in
         case 1: return scalar_mul_c<BnG2, BnFr>(base, scalar, out, normalize);
         case 2: return scalar_mul_c<BlsG1, BlsFr>(base, scalar, out, normalize);
         case 3: return scalar_mul_c<Bw6G1, Bw6Fr>(base, scalar, out, normalize);
+        case 4: return scalar_mul_c<BlsG2, BlsFr>(base, scalar, out, normalize);
+        case 5: return scalar_mul_c<Bw6G2, Bw6Fr>(base, scalar, out, normalize);
+        case 6: return scalar_mul_c<Bls381G1, Bls381Fr>(base, scalar, out, normalize);
+        case 7: return scalar_mul_c<Bls381G2, Bls381Fr>(base, scalar, out, normalize);
     }
 }
 // method: 0 BDLO12, 1 BDLO12_signed; form: 0 normal, 1 special.  Returns seconds inside multi_exp.
@@ -1035,6 +1105,10 @@ void orc_batch_to_special(int gid, void *inout, size_t n) {
         case 1: return to_special_c<BnG2>(inout, n);
         case 2: return to_special_c<BlsG1>(inout, n);
         case 3: return to_special_c<Bw6G1>(inout, n);
+        case 4: return to_special_c<BlsG2>(inout, n);
+        case 5: return to_special_c<Bw6G2>(inout, n);
+        case 6: return to_special_c<Bls381G1>(inout, n);
+        case 7: return to_special_c<Bls381G2>(inout, n);
     }
 }
 size_t orc_window_table_rows(int gid, size_t scalar_bits, size_t window) {
@@ -1048,6 +1122,10 @@ void orc_window_table(int gid, size_t scalar_bits, size_t window, const void *g,
         case 1: return window_table_c<BnG2>(scalar_bits, window, g, out);
         case 2: return window_table_c<BlsG1>(scalar_bits, window, g, out);
         case 3: return window_table_c<Bw6G1>(scalar_bits, window, g, out);
+        case 4: return window_table_c<BlsG2>(scalar_bits, window, g, out);
+        case 5: return window_table_c<Bw6G2>(scalar_bits, window, g, out);
+        case 6: return window_table_c<Bls381G1>(scalar_bits, window, g, out);
+        case 7: return window_table_c<Bls381G2>(scalar_bits, window, g, out);
     }
 }
 double orc_batch_exp(int gid, size_t scalar_bits, size_t window, const void *table, size_t rows,
@@ -1058,6 +1136,10 @@ double orc_batch_exp(int gid, size_t scalar_bits, size_t window, const void *tab
         case 1: return batch_exp_c<BnG2, BnFr>(scalar_bits, window, table, rows, row_len, scalars, n, out, normalize);
         case 2: return batch_exp_c<BlsG1, BlsFr>(scalar_bits, window, table, rows, row_len, scalars, n, out, normalize);
         case 3: return batch_exp_c<Bw6G1, Bw6Fr>(scalar_bits, window, table, rows, row_len, scalars, n, out, normalize);
+        case 4: return batch_exp_c<BlsG2, BlsFr>(scalar_bits, window, table, rows, row_len, scalars, n, out, normalize);
+        case 5: return batch_exp_c<Bw6G2, Bw6Fr>(scalar_bits, window, table, rows, row_len, scalars, n, out, normalize);
+        case 6: return batch_exp_c<Bls381G1, Bls381Fr>(scalar_bits, window, table, rows, row_len, scalars, n, out, normalize);
+        case 7: return batch_exp_c<Bls381G2, Bls381Fr>(scalar_bits, window, table, rows, row_len, scalars, n, out, normalize);
     }
     return -1.0;
 }
@@ -1072,6 +1154,10 @@ void orc_group_eq(int gid, const void *a, const void *b, uint8_t *out, size_t n)
         case 1: return group_eq_c<BnG2>(a, b, out, n);
         case 2: return group_eq_c<BlsG1>(a, b, out, n);
         case 3: return group_eq_c<Bw6G1>(a, b, out, n);
+        case 4: return group_eq_c<BlsG2>(a, b, out, n);
+        case 5: return group_eq_c<Bw6G2>(a, b, out, n);
+        case 6: return group_eq_c<Bls381G1>(a, b, out, n);
+        case 7: return group_eq_c<Bls381G2>(a, b, out, n);
     }
 }
 void orc_group_constants(int gid, void *zero, void *one) {
@@ -1081,17 +1167,23 @@ void orc_group_constants(int gid, void *zero, void *one) {
         case 1: store_point((uint64_t *)zero, BnG2::zero()); store_point((uint64_t *)one, g_bn_g2); break;
         case 2: store_point((uint64_t *)zero, BlsG1::zero()); store_point((uint64_t *)one, g_bls_g1); break;
         case 3: store_point((uint64_t *)zero, Bw6G1::zero()); store_point((uint64_t *)one, g_bw6_g1); break;
+        case 4: store_point((uint64_t *)zero, BlsG2::zero()); store_point((uint64_t *)one, g_bls_g2); break;
+        case 5: store_point((uint64_t *)zero, Bw6G2::zero()); store_point((uint64_t *)one, g_bw6_g2); break;
+        case 6: store_point((uint64_t *)zero, Bls381G1::zero()); store_point((uint64_t *)one, g_bls381_g1); break;
+        case 7: store_point((uint64_t *)zero, Bls381G2::zero()); store_point((uint64_t *)one, g_bls381_g2); break;
     }
 }
 size_t orc_field_bytes(int fid) {
-    static const size_t b[7] = {32, 32, 48, 32, 96, 48, 64};
-    return fid >= 0 && fid < 7 ? b[fid] : 0;
+    static const size_t b[11] = {32, 32, 48, 32, 96, 48, 64, 96, 48, 32, 96};
+    return fid >= 0 && fid < 11 ? b[fid] : 0;
 }
 void orc_field_op(int fid, int op, const void *a, const void *b, void *out, size_t n) {
     init_all();
     const uint64_t *pa = (const uint64_t *)a, *pb = (const uint64_t *)b;
     uint64_t *po = (uint64_t *)out;
     if (fid == 6) return field_op<BnFq2>(op, pa, pb, po, n);
+    if (fid == 7) return field_op<BlsFq2>(op, pa, pb, po, n);
+    if (fid == 10) return field_op<Bls381Fq2>(op, pa, pb, po, n);
     if (op >= 6) {
         FIELD_SWITCH(fid, field_convert<F>(op, pa, po, n));
     } else {

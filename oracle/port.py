@@ -22,9 +22,14 @@ BDLO12, BDLO12_SIGNED = 0, 1
 FORM_NORMAL, FORM_SPECIAL = 0, 1
 # field ids of ref_field_op
 F_ALT_BN128_FQ, F_ALT_BN128_FR, F_BLS12_377_FQ, F_BLS12_377_FR, F_BW6_761_FQ, F_BW6_761_FR, \
-    F_ALT_BN128_FQ2 = range(7)
-FR_OF_GROUP = {0: F_ALT_BN128_FR, 1: F_ALT_BN128_FR, 2: F_BLS12_377_FR, 3: F_BW6_761_FR}
-FQ_OF_GROUP = {0: F_ALT_BN128_FQ, 1: F_ALT_BN128_FQ2, 2: F_BLS12_377_FQ, 3: F_BW6_761_FQ}
+    F_ALT_BN128_FQ2, F_BLS12_377_FQ2, F_BLS12_381_FQ, F_BLS12_381_FR, F_BLS12_381_FQ2 = range(11)
+FR_OF_GROUP = {0: F_ALT_BN128_FR, 1: F_ALT_BN128_FR, 2: F_BLS12_377_FR, 3: F_BW6_761_FR,
+               4: F_BLS12_377_FR, 5: F_BW6_761_FR, 6: F_BLS12_381_FR, 7: F_BLS12_381_FR}
+FQ_OF_GROUP = {0: F_ALT_BN128_FQ, 1: F_ALT_BN128_FQ2, 2: F_BLS12_377_FQ, 3: F_BW6_761_FQ,
+               4: F_BLS12_377_FQ2, 5: F_BW6_761_FQ, 6: F_BLS12_381_FQ, 7: F_BLS12_381_FQ2}
+FQ2_FIELDS = (F_ALT_BN128_FQ2, F_BLS12_377_FQ2, F_BLS12_381_FQ2)
+FQ2_BASE = {F_ALT_BN128_FQ2: F_ALT_BN128_FQ, F_BLS12_377_FQ2: F_BLS12_377_FQ,
+            F_BLS12_381_FQ2: F_BLS12_381_FQ}
 OP_MUL, OP_SQR, OP_ADD, OP_SUB, OP_NEG, OP_INV, OP_TO_PLAIN, OP_FROM_PLAIN = range(8)
 G_ADD, G_ADD_FN, G_MIXED_ADD, G_DBL, G_NEG, G_TO_AFFINE = range(6)
 

@@ -76,6 +76,13 @@ BW6_761_Q = PrimeField(
     0x122E824FB83CE0AD187C94004FAFF3EB926186A81D14688528275EF8087BE41707BA638E584E91903CEBAFF25B423048689C8ED12F9FD9071DCD3DC73EBFF2E98A116C25667A8F8160CF8AEEAF0A437E6913E6870000082F49D00000000008B,
     12)
 
+BLS12_381_R = PrimeField(
+    "bls12_381_Fr", 0x73EDA753299D7D483339D80809A1D80553BDA402FFFE5BFEFFFFFFFF00000001, 4)
+BLS12_381_Q = PrimeField(
+    "bls12_381_Fq",
+    0x1A0111EA397FE69A4B1BA7B6434BACD764774B84F38512BF6730D2A0F6B0F6241EABFFFEB153FFFFB9FEFFFFFFFFAAAB,
+    6)
+
 # ----------------------------------------------------------------------------------------------
 # Element arithmetic: coordinates are ints (degree 1) or 2-tuples (Fq2 = Fq[u]/(u^2 - nr)).
 
@@ -341,7 +348,43 @@ BW6_761_G1 = Group(
      2101735126520897423911504562215834951148127555913367997162789335052900271653517958562461315794228241561913734371411178226936527683203879553093934185950470971848972085321797958124416462268292467002957525517188485984766314758624099),
     BW6_761_Q.p - 1, True)
 
-GROUPS = [ALT_BN128_G1, ALT_BN128_G2, BLS12_377_G1, BW6_761_G1]
+# The remaining groups of the same families; generators as the compiled
+# reference reports them (bls12_377_init.cpp:392-420, bw6_761_init.cpp:340-360,
+# bls12_381_init.cpp:441-450, 517-534).
+_KQ2_BLS = Fq2Ops(BLS12_377_Q, BLS12_377_Q.p - 5)  # bls12_377_init.cpp:170-176
+_KQ_381 = Fq1Ops(BLS12_381_Q)
+_KQ2_381 = Fq2Ops(BLS12_381_Q, BLS12_381_Q.p - 1)  # bls12_381_init.cpp:137-139
+
+BLS12_377_G2 = Group(
+    4, "bls12_377_G2", BLS12_377_R, BLS12_377_Q, _KQ2_BLS,
+    ((0xb997fef930828fe1b9e6a1707b8aa508a3dbfd7fe2246499c709226a0a6fef49f85b3a375363f4f8f6ea3fbd159f8a,
+      0xd6ac33b84947d9845f81a57a136bfa326e915fabc8cd6a57ff133b42d00f62e4e1af460228cd5184deae976fa62596),
+     (0x118dd509b2e9a13744a507d515a595dbb7e3b63df568866473790184bdf83636c94df2b7a962cb2af4337f07cb7e622,
+      0x185067c6ca76d992f064a432bd9f9be832b0cac2d824d0518f77d39e76c3e146afb825f2092218d038867d7f337a010)),
+    _KQ2_BLS.inv((0, 1)), False)  # y^2 = x^3 + 1/u, bls12_377_init.cpp:302-304
+
+BW6_761_G2 = Group(
+    5, "bw6_761_G2", BW6_761_R, BW6_761_Q, _KQ_BW6,
+    (0x110133241d9b816c852a82e69d660f9d61053aac5a7115f4c06201013890f6d26b41c5dab3da268734ec3f1f09feb58c5bbcae9ac70e7c7963317a300e1b6bace6948cb3cd208d700e96efbc2ad54b06410cf4fe1bf995ba830c194cd025f1c,
+     0x17c3357761369f8179eb10e4b6d2dc26b7cf9acec2181c81a78e2753ffe3160a1d86c80b95a59c94c97eb733293fef64f293dbd2c712b88906c170ffa823003ea96fcd504affc758aa2d3a3c5a02a591ec0594f9eac689eb70a16728c73b61),
+    4, True)  # y^2 = x^3 + 4, bw6_761_init.cpp:272-282
+
+BLS12_381_G1 = Group(
+    6, "bls12_381_G1", BLS12_381_R, BLS12_381_Q, _KQ_381,
+    (0x17f1d3a73197d7942695638c4fa9ac0fc3688c4f9774b905a14e3a3f171bac586c55e83ff97a1aeffb3af00adb22c6bb,
+     0x8b3f481e3aaa0f1a09e30ed741d8ae4fcf5e095d5d00af600db18cb2c04b3edd03cc744a2888ae40caa232946c5e7e1),
+    4, False)
+
+BLS12_381_G2 = Group(
+    7, "bls12_381_G2", BLS12_381_R, BLS12_381_Q, _KQ2_381,
+    ((0x24aa2b2f08f0a91260805272dc51051c6e47ad4fa403b02b4510b647ae3d1770bac0326a805bbefd48056c8c121bdb8,
+      0x13e02b6052719f607dacd3a088274f65596bd0d09920b61ab5da61bbdc7f5049334cf11213945d57e5ac7d055d042b7e),
+     (0xce5d527727d6e118cc9cdc6da2e351aadfd9baa8cbdd3a76d429a695160d12c923ac9cc3baca289e193548608b82801,
+      0x606c4a02ea734cc32acd2b02bc28b99cb3e287e85a763af267492ab572e99ab3f370d275cec1da1aaa9075ff05f79be)),
+    (4, 4), False)  # y^2 = x^3 + 4 (1 + u), bls12_381_init.cpp:418-420
+
+GROUPS = [ALT_BN128_G1, ALT_BN128_G2, BLS12_377_G1, BW6_761_G1,
+          BLS12_377_G2, BW6_761_G2, BLS12_381_G1, BLS12_381_G2]
 GROUP_BY_NAME = {g.name: g for g in GROUPS}
 
 # ----------------------------------------------------------------------------------------------

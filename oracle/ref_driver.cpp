@@ -26,6 +26,7 @@
 
 #include <libff/algebra/curves/alt_bn128/alt_bn128_pp.hpp>
 #include <libff/algebra/curves/bls12_377/bls12_377_pp.hpp>
+#include <libff/algebra/curves/bls12_381/bls12_381_pp.hpp>
 #include <libff/algebra/curves/bw6_761/bw6_761_pp.hpp>
 #include <libff/algebra/fields/field_utils.hpp>
 #include <libff/algebra/scalar_multiplication/multiexp.hpp>
@@ -45,7 +46,16 @@ using namespace libff;
 namespace
 {
 
-enum group_id { G_ALT_BN128_G1 = 0, G_ALT_BN128_G2 = 1, G_BLS12_377_G1 = 2, G_BW6_761_G1 = 3 };
+enum group_id {
+    G_ALT_BN128_G1 = 0,
+    G_ALT_BN128_G2 = 1,
+    G_BLS12_377_G1 = 2,
+    G_BW6_761_G1 = 3,
+    G_BLS12_377_G2 = 4,
+    G_BW6_761_G2 = 5,
+    G_BLS12_381_G1 = 6,
+    G_BLS12_381_G2 = 7
+};
 enum field_id {
     F_ALT_BN128_FQ = 0,
     F_ALT_BN128_FR = 1,
@@ -53,7 +63,11 @@ enum field_id {
     F_BLS12_377_FR = 3,
     F_BW6_761_FQ = 4,
     F_BW6_761_FR = 5,
-    F_ALT_BN128_FQ2 = 6
+    F_ALT_BN128_FQ2 = 6,
+    F_BLS12_377_FQ2 = 7,
+    F_BLS12_381_FQ = 8,
+    F_BLS12_381_FR = 9,
+    F_BLS12_381_FQ2 = 10
 };
 
 template<typename T> std::vector<T> load_vec(const void *p, size_t n)
@@ -256,6 +270,10 @@ typedef ops<alt_bn128_G1, alt_bn128_Fr> O0;
 typedef ops<alt_bn128_G2, alt_bn128_Fr> O1;
 typedef ops<bls12_377_G1, bls12_377_Fr> O2;
 typedef ops<bw6_761_G1, bw6_761_Fr> O3;
+typedef ops<bls12_377_G2, bls12_377_Fr> O4;
+typedef ops<bw6_761_G2, bw6_761_Fr> O5;
+typedef ops<bls12_381_G1, bls12_381_Fr> O6;
+typedef ops<bls12_381_G2, bls12_381_Fr> O7;
 
 // op: 0 mul, 1 sqr, 2 add, 3 sub, 4 neg, 5 inverse, 6 as_bigint (mont->plain),
 //     7 from bigint (plain->mont)
@@ -318,6 +336,7 @@ int ref_init()
         alt_bn128_pp::init_public_params();
         bls12_377_pp::init_public_params();
         bw6_761_pp::init_public_params();
+        bls12_381_pp::init_public_params();
         g_inited = true;
     }
     return 1;
@@ -348,6 +367,10 @@ size_t ref_group_bytes(int gid)
     case 1: return sizeof(alt_bn128_G2);
     case 2: return sizeof(bls12_377_G1);
     case 3: return sizeof(bw6_761_G1);
+    case 4: return sizeof(bls12_377_G2);
+    case 5: return sizeof(bw6_761_G2);
+    case 6: return sizeof(bls12_381_G1);
+    case 7: return sizeof(bls12_381_G2);
     }
     return 0;
 }
@@ -359,6 +382,10 @@ size_t ref_scalar_bytes(int gid)
     case 1: return sizeof(alt_bn128_Fr);
     case 2: return sizeof(bls12_377_Fr);
     case 3: return sizeof(bw6_761_Fr);
+    case 4: return sizeof(bls12_377_Fr);
+    case 5: return sizeof(bw6_761_Fr);
+    case 6: return sizeof(bls12_381_Fr);
+    case 7: return sizeof(bls12_381_Fr);
     }
     return 0;
 }
@@ -370,6 +397,10 @@ size_t ref_scalar_bits(int gid)
     case 1: return alt_bn128_Fr::size_in_bits();
     case 2: return bls12_377_Fr::size_in_bits();
     case 3: return bw6_761_Fr::size_in_bits();
+    case 4: return bls12_377_Fr::size_in_bits();
+    case 5: return bw6_761_Fr::size_in_bits();
+    case 6: return bls12_381_Fr::size_in_bits();
+    case 7: return bls12_381_Fr::size_in_bits();
     }
     return 0;
 }
@@ -380,6 +411,10 @@ size_t ref_scalar_bits(int gid)
     case 1: return O1::CALL;                                                                       \
     case 2: return O2::CALL;                                                                       \
     case 3: return O3::CALL;                                                                       \
+    case 4: return O4::CALL;                                                                       \
+    case 5: return O5::CALL;                                                                       \
+    case 6: return O6::CALL;                                                                       \
+    case 7: return O7::CALL;                                                                       \
     }
 
 void ref_gen_scalars(int gid, uint64_t start, size_t n, void *out)
@@ -442,6 +477,10 @@ size_t ref_exp_window_size(int gid, size_t n)
     case 1: return get_exp_window_size<alt_bn128_G2>(n);
     case 2: return get_exp_window_size<bls12_377_G1>(n);
     case 3: return get_exp_window_size<bw6_761_G1>(n);
+    case 4: return get_exp_window_size<bls12_377_G2>(n);
+    case 5: return get_exp_window_size<bw6_761_G2>(n);
+    case 6: return get_exp_window_size<bls12_381_G1>(n);
+    case 7: return get_exp_window_size<bls12_381_G2>(n);
     }
     return 0;
 }
@@ -471,6 +510,10 @@ size_t ref_field_bytes(int fid)
     case F_BW6_761_FQ: return sizeof(bw6_761_Fq);
     case F_BW6_761_FR: return sizeof(bw6_761_Fr);
     case F_ALT_BN128_FQ2: return sizeof(alt_bn128_Fq2);
+    case F_BLS12_377_FQ2: return sizeof(bls12_377_Fq2);
+    case F_BLS12_381_FQ: return sizeof(bls12_381_Fq);
+    case F_BLS12_381_FR: return sizeof(bls12_381_Fr);
+    case F_BLS12_381_FQ2: return sizeof(bls12_381_Fq2);
     }
     return 0;
 }
@@ -485,6 +528,8 @@ void ref_field_op(int fid, int op, const void *a, const void *b, void *out, size
         case F_BLS12_377_FR: return field_convert<bls12_377_Fr>(op, a, out, n);
         case F_BW6_761_FQ: return field_convert<bw6_761_Fq>(op, a, out, n);
         case F_BW6_761_FR: return field_convert<bw6_761_Fr>(op, a, out, n);
+        case F_BLS12_381_FQ: return field_convert<bls12_381_Fq>(op, a, out, n);
+        case F_BLS12_381_FR: return field_convert<bls12_381_Fr>(op, a, out, n);
         }
         return;
     }
@@ -496,6 +541,10 @@ void ref_field_op(int fid, int op, const void *a, const void *b, void *out, size
     case F_BW6_761_FQ: return field_op<bw6_761_Fq>(op, a, b, out, n);
     case F_BW6_761_FR: return field_op<bw6_761_Fr>(op, a, b, out, n);
     case F_ALT_BN128_FQ2: return field_op<alt_bn128_Fq2>(op, a, b, out, n);
+    case F_BLS12_377_FQ2: return field_op<bls12_377_Fq2>(op, a, b, out, n);
+    case F_BLS12_381_FQ: return field_op<bls12_381_Fq>(op, a, b, out, n);
+    case F_BLS12_381_FR: return field_op<bls12_381_Fr>(op, a, b, out, n);
+    case F_BLS12_381_FQ2: return field_op<bls12_381_Fq2>(op, a, b, out, n);
     }
 }
 
@@ -505,6 +554,7 @@ long ref_signed_digit(int fid, const void *scalar_mont, size_t c, size_t idx)
     case F_ALT_BN128_FR: return signed_digit<alt_bn128_Fr>(scalar_mont, c, idx);
     case F_BLS12_377_FR: return signed_digit<bls12_377_Fr>(scalar_mont, c, idx);
     case F_BW6_761_FR: return signed_digit<bw6_761_Fr>(scalar_mont, c, idx);
+    case F_BLS12_381_FR: return signed_digit<bls12_381_Fr>(scalar_mont, c, idx);
     }
     return 0;
 }
@@ -515,6 +565,7 @@ size_t ref_num_signed_digits(int fid, size_t c)
     case F_ALT_BN128_FR: return field_get_num_signed_digits<alt_bn128_Fr>(c);
     case F_BLS12_377_FR: return field_get_num_signed_digits<bls12_377_Fr>(c);
     case F_BW6_761_FR: return field_get_num_signed_digits<bw6_761_Fr>(c);
+    case F_BLS12_381_FR: return field_get_num_signed_digits<bls12_381_Fr>(c);
     }
     return 0;
 }
@@ -580,6 +631,10 @@ size_t ref_wire_group_write(int gid, const void *in, void *out, size_t n)
     case 1: return wire_group_write<alt_bn128_G2>(in, out, n);
     case 2: return wire_group_write<bls12_377_G1>(in, out, n);
     case 3: return wire_group_write<bw6_761_G1>(in, out, n);
+    case 4: return wire_group_write<bls12_377_G2>(in, out, n);
+    case 5: return wire_group_write<bw6_761_G2>(in, out, n);
+    case 6: return wire_group_write<bls12_381_G1>(in, out, n);
+    case 7: return wire_group_write<bls12_381_G2>(in, out, n);
     }
     return 0;
 }
@@ -590,6 +645,10 @@ size_t ref_wire_group_read(int gid, const void *in, void *out, uint8_t *okv, siz
     case 1: return wire_group_read<alt_bn128_G2>(in, out, okv, n);
     case 2: return wire_group_read<bls12_377_G1>(in, out, okv, n);
     case 3: return wire_group_read<bw6_761_G1>(in, out, okv, n);
+    case 4: return wire_group_read<bls12_377_G2>(in, out, okv, n);
+    case 5: return wire_group_read<bw6_761_G2>(in, out, okv, n);
+    case 6: return wire_group_read<bls12_381_G1>(in, out, okv, n);
+    case 7: return wire_group_read<bls12_381_G2>(in, out, okv, n);
     }
     return 0;
 }
@@ -599,6 +658,9 @@ size_t ref_wire_scalar_write(int gid, const void *in, void *out, size_t n)
     case 0: case 1: return wire_field_write<alt_bn128_Fr>(in, out, n);
     case 2: return wire_field_write<bls12_377_Fr>(in, out, n);
     case 3: return wire_field_write<bw6_761_Fr>(in, out, n);
+    case 4: return wire_field_write<bls12_377_Fr>(in, out, n);
+    case 5: return wire_field_write<bw6_761_Fr>(in, out, n);
+    case 6: case 7: return wire_field_write<bls12_381_Fr>(in, out, n);
     }
     return 0;
 }
@@ -608,6 +670,9 @@ size_t ref_wire_scalar_read(int gid, const void *in, void *out, uint8_t *okv, si
     case 0: case 1: return wire_field_read<alt_bn128_Fr>(in, out, okv, n);
     case 2: return wire_field_read<bls12_377_Fr>(in, out, okv, n);
     case 3: return wire_field_read<bw6_761_Fr>(in, out, okv, n);
+    case 4: return wire_field_read<bls12_377_Fr>(in, out, okv, n);
+    case 5: return wire_field_read<bw6_761_Fr>(in, out, okv, n);
+    case 6: case 7: return wire_field_read<bls12_381_Fr>(in, out, okv, n);
     }
     return 0;
 }

@@ -19,16 +19,18 @@ from oracle import ref  # noqa: E402
 
 OUT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "reference_vectors.npz")
 FIELD_NAMES = ["alt_bn128_fq", "alt_bn128_fr", "bls12_377_fq", "bls12_377_fr", "bw6_761_fq",
-               "bw6_761_fr", "alt_bn128_fq2"]
+               "bw6_761_fr", "alt_bn128_fq2", "bls12_377_fq2", "bls12_381_fq", "bls12_381_fr",
+               "bls12_381_fq2"]
 FIELD_MODEL = [pm.ALT_BN128_Q, pm.ALT_BN128_R, pm.BLS12_377_Q, pm.BLS12_377_R, pm.BW6_761_Q,
-               pm.BW6_761_R, pm.ALT_BN128_Q]
+               pm.BW6_761_R, pm.ALT_BN128_Q, pm.BLS12_377_Q, pm.BLS12_381_Q, pm.BLS12_381_R,
+               pm.BLS12_381_Q]
 MSM_SIZES = [0, 1, 2, 3, 5, 64, 257, 1000]
 
 
 def field_elements(fid, count=10):
     """Montgomery-form elements: 0, 1, p-1, 2, then SHA512_rng-style pseudo-random values."""
     f = FIELD_MODEL[fid]
-    deg = 2 if fid == ref.F_ALT_BN128_FQ2 else 1
+    deg = 2 if fid in ref.FQ2_FIELDS else 1
     vals = [0, 1, f.p - 1, 2] + [pm.sha512_rng(f, 7000 + 31 * fid + i) for i in range(count * deg)]
     rows = []
     for i in range(count):
@@ -54,15 +56,16 @@ def main():
             out[f"field/{name}/{opname}"] = ref.field_op(fid, op, a, b)
         nz = a[1:]  # inverse of zero is undefined in the reference
         out[f"field/{name}/inv"] = ref.field_op(fid, ref.OP_INV, nz)
-        if fid != ref.F_ALT_BN128_FQ2:
+        if fid not in ref.FQ2_FIELDS:
             out[f"field/{name}/to_plain"] = ref.field_op(fid, ref.OP_TO_PLAIN, a)
     # ---- scalar generator, digits, window size
-    for gid in range(4):
+    for gid in range(8):
         idx = [0, 1, 2, 5]
         out[f"rng/{gid}/first"] = ref.gen_scalars(gid, 6)
         out[f"rng/{gid}/walk_params"] = ref.gen_scalars(gid, 2, start=1 << 63)
-    for fid in (ref.F_ALT_BN128_FR, ref.F_BLS12_377_FR, ref.F_BW6_761_FR):
-        g = {ref.F_ALT_BN128_FR: 0, ref.F_BLS12_377_FR: 2, ref.F_BW6_761_FR: 3}[fid]
+    for fid in (ref.F_ALT_BN128_FR, ref.F_BLS12_377_FR, ref.F_BW6_761_FR, ref.F_BLS12_381_FR):
+        g = {ref.F_ALT_BN128_FR: 0, ref.F_BLS12_377_FR: 2, ref.F_BW6_761_FR: 3,
+             ref.F_BLS12_381_FR: 6}[fid]
         f = FIELD_MODEL[fid]
         G = pm.GROUPS[g]
         sc = np.concatenate([G.encode_scalars([f.p - 1, f.p - 2, 0, 1, (1 << 200) - 1, 0x79D69]),
@@ -78,7 +81,7 @@ def main():
     out["pippenger_c/n"] = np.array(ns, dtype=np.uint64)
     out["pippenger_c/c"] = np.array([ref.pippenger_optimal_c(n) for n in ns], dtype=np.uint64)
     # ---- group law (raw representatives) incl. the exceptional cases
-    for gid in range(4):
+    for gid in range(8):
         zero, one = ref.group_constants(gid)
         P = ref.gen_bases_walk(gid, 6)
         J = ref.group_op(gid, ref.G_ADD, P[:5], P[1:6])      # non-normalised points
@@ -99,7 +102,7 @@ def main():
         out[f"group/{gid}/walk_bases"] = ref.gen_bases_walk(gid, 8)
         out[f"group/{gid}/walk_bases_at_5000"] = ref.gen_bases_walk(gid, 3, start=5000)
     # ---- multi_exp on the synthetic workload (gen_scalars + gen_bases_walk), affine results
-    for gid in range(4):
+    for gid in range(8):
         for n in MSM_SIZES:
             if gid == 3 and n > 300:
                 continue
@@ -115,7 +118,7 @@ def main():
         out[f"msm_raw/{gid}/64/special"] = ref.multi_exp(gid, bases, scalars, form=1, normalize=False)
         out[f"msm_raw/{gid}/64/normal"] = ref.multi_exp(gid, bases, scalars, form=0, normalize=False)
     # ---- exceptional inputs (SURVEY.md §8d edge-case suite)
-    for gid in range(4):
+    for gid in range(8):
         G = pm.GROUPS[gid]
         r = G.fr.p
         zero, _ = ref.group_constants(gid)
@@ -148,7 +151,7 @@ def main():
     out["edge_case1/bases"], out["edge_case1/scalars"] = eb, es
     out["edge_case1/result"] = ref.multi_exp(0, eb, es, method=ref.BDLO12_SIGNED, form=ref.FORM_NORMAL)
     # ---- batch_to_special and batch_exp
-    for gid in range(4):
+    for gid in range(8):
         P = ref.gen_bases_walk(gid, 13)
         J = ref.group_op(gid, ref.G_ADD, P[:12], P[1:13])
         zero, one = ref.group_constants(gid)
@@ -166,7 +169,7 @@ def main():
         out[f"batch_exp/{gid}/out_raw"] = ref.batch_exp(gid, bits, window, table, sc, normalize=False)[1]
         out[f"batch_exp/{gid}/out"] = ref.batch_exp(gid, bits, window, table, sc, normalize=True)[1]
     # ---- wire format of the reference's ffi layer (ffi/ffi_serialization.tcc:98-187)
-    for gid in range(4):
+    for gid in range(8):
         zero, one = ref.group_constants(gid)
         P = ref.gen_bases_walk(gid, 3)
         J = ref.group_op(gid, ref.G_ADD, P[:2], P[1:3])  # non-normalised: the writer normalises
@@ -181,7 +184,7 @@ def main():
     print("wrote", OUT, os.path.getsize(OUT), "bytes,", len(out), "arrays")
 
 
-G_BITS = {0: 254, 1: 254, 2: 253, 3: 377}
+G_BITS = {0: 254, 1: 254, 2: 253, 3: 377, 4: 253, 5: 377, 6: 255, 7: 255}
 
 if __name__ == "__main__":
     main()

@@ -32,9 +32,9 @@ def test_library_exports_every_declared_symbol():
 
 def test_size_queries_match_reference_sizeof():
     """sizeof(GroupT) / sizeof(Fr) of the reference (SURVEY.md §8 sizes table)."""
-    assert [m.group_bytes(g) for g in range(4)] == [96, 192, 144, 288]
-    assert [m.scalar_bytes(g) for g in range(4)] == [32, 32, 32, 48]
-    assert m.group_bytes(7) == 0 and m.scalar_bytes(7) == 0
+    assert [m.group_bytes(g) for g in range(8)] == [96, 192, 144, 288, 288, 288, 144, 288]
+    assert [m.scalar_bytes(g) for g in range(8)] == [32, 32, 32, 48, 32, 48, 32, 32]
+    assert m.group_bytes(8) == 0 and m.scalar_bytes(8) == 0
 
 
 def test_shard_range_is_the_reference_chunk_split():

@@ -7,7 +7,7 @@ import pytest
 from oracle import pymodel as pm
 
 pytestmark = pytest.mark.gpu
-GROUPS = [0, 1, 2, 3]
+GROUPS = [0, 1, 2, 3, 4, 5, 6, 7]
 
 
 def rand_field(ref, fid, n, seed):
@@ -18,10 +18,10 @@ def rand_field(ref, fid, n, seed):
         rng.integers(0, 2, size=(n, words), dtype=np.uint64)
     # reduce through the reference itself: x -> x * 1 keeps it canonical (mul_reduce output < p)
     a[:, -1] &= np.uint64(0x00FFFFFFFFFFFFFF)
-    if fid == ref.F_ALT_BN128_FQ2:
+    if fid in ref.FQ2_FIELDS:
         a[:, words // 2 - 1] &= np.uint64(0x00FFFFFFFFFFFFFF)
     one = ref.field_op(fid, ref.OP_FROM_PLAIN, np.tile(np.eye(1, words, 0, dtype=np.uint64), (n, 1))) \
-        if fid != ref.F_ALT_BN128_FQ2 else None
+        if fid not in ref.FQ2_FIELDS else None
     return ref.field_op(fid, ref.OP_MUL, a, one) if one is not None else ref.field_op(fid, ref.OP_ADD, ref.field_op(fid, ref.OP_SQR, a), a)
 
 
@@ -95,11 +95,11 @@ def test_shared_reduction_product_and_squaring(engine, ref, gid):
 def _one(ref, fid):
     """Montgomery one of field fid as a (1, words) array (Fq2: (1, 0))."""
     words = ref.lib().ref_field_bytes(fid) // 8
-    if fid == ref.F_ALT_BN128_FQ2:
+    if fid in ref.FQ2_FIELDS:
         half = words // 2
         plain = np.zeros((1, half), dtype=np.uint64)
         plain[0, 0] = 1
-        one = ref.field_op(ref.F_ALT_BN128_FQ, ref.OP_FROM_PLAIN, plain)
+        one = ref.field_op(ref.FQ2_BASE[fid], ref.OP_FROM_PLAIN, plain)
         return np.concatenate([one, np.zeros_like(one)], axis=1)
     plain = np.zeros((1, words), dtype=np.uint64)
     plain[0, 0] = 1

@@ -8,8 +8,8 @@ from oracle import pymodel as pm
 
 pytestmark = pytest.mark.gpu
 
-GROUPS = [0, 1, 2, 3]
-SMALL_N = {0: 1000, 1: 300, 2: 500, 3: 200}
+GROUPS = [0, 1, 2, 3, 4, 5, 6, 7]
+SMALL_N = {0: 1000, 1: 300, 2: 500, 3: 200, 4: 200, 5: 200, 6: 500, 7: 200}
 
 
 def affine(ref, gid, pts):
@@ -259,7 +259,7 @@ def test_multi_exp_pipelined_upload(engine, ref, gid, parts):
     """Host-buffer calls cut the point range into `h2d_parts` independently uploaded and computed
     ranges (upload of range k + 1 under the MSM of range k); the sum of the partial results is the
     same element (multiexp.tcc:663-687 does the same split across threads)."""
-    n = {0: 1003, 1: 301, 2: 502, 3: 99}[gid]
+    n = {0: 1003, 1: 301, 2: 502, 3: 99, 4: 99, 5: 99, 6: 502, 7: 99}[gid]
     aff = ref.gen_bases_walk(gid, n + 1)
     jac = ref.group_op(gid, ref.G_ADD, aff[:-1], aff[1:])
     scalars = ref.gen_scalars(gid, n, start=21)
@@ -280,7 +280,7 @@ def test_multi_exp_groth16_shaped_scalars(engine, ref, gid):
     pile into one bucket of the lowest window, and the windows above the longest scalar are
     dropped from the reduction (the reference sizes its loop by num_bits, multiexp.tcc:298-306)."""
     g = pm.GROUPS[gid]
-    n = {0: 2000, 1: 400, 2: 800, 3: 150}[gid]
+    n = {0: 2000, 1: 400, 2: 800, 3: 150, 4: 150, 5: 150, 6: 800, 7: 150}[gid]
     rng = np.random.RandomState(5 + gid)
     kinds = rng.choice(4, size=n, p=[0.55, 0.3, 0.1, 0.05])
     full = g.decode_scalars(ref.gen_scalars(gid, n, start=300))

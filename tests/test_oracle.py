@@ -18,10 +18,12 @@ from oracle import pymodel as pm
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 FIELD_NAMES = ["alt_bn128_fq", "alt_bn128_fr", "bls12_377_fq", "bls12_377_fr", "bw6_761_fq",
-               "bw6_761_fr", "alt_bn128_fq2"]
-GROUPS = [0, 1, 2, 3]
-SCALAR_FIELD = {0: port.F_ALT_BN128_FR, 1: port.F_ALT_BN128_FR, 2: port.F_BLS12_377_FR,
-                3: port.F_BW6_761_FR}
+               "bw6_761_fr", "alt_bn128_fq2", "bls12_377_fq2", "bls12_381_fq", "bls12_381_fr",
+               "bls12_381_fq2"]
+PRIME_FIELDS = {0: pm.ALT_BN128_Q, 1: pm.ALT_BN128_R, 2: pm.BLS12_377_Q, 3: pm.BLS12_377_R,
+                4: pm.BW6_761_Q, 5: pm.BW6_761_R, 8: pm.BLS12_381_Q, 9: pm.BLS12_381_R}
+GROUPS = [0, 1, 2, 3, 4, 5, 6, 7]
+SCALAR_FIELD = port.FR_OF_GROUP
 
 
 @pytest.fixture(scope="module")
@@ -41,7 +43,7 @@ def live_ref():
 # ------------------------------------------------------------------------------------------------
 # fields (fp.tcc / fp2.tcc)
 
-@pytest.mark.parametrize("fid", range(7))
+@pytest.mark.parametrize("fid", range(11))
 def test_port_field_ops_match_reference(golden, fid):
     name = FIELD_NAMES[fid]
     a, b = golden[f"field/{name}/a"], golden[f"field/{name}/b"]
@@ -50,17 +52,16 @@ def test_port_field_ops_match_reference(golden, fid):
         np.testing.assert_array_equal(port.field_op(fid, op, a, b), golden[f"field/{name}/{opname}"],
                                       err_msg=f"{name} {opname}")
     np.testing.assert_array_equal(port.field_op(fid, port.OP_INV, a[1:]), golden[f"field/{name}/inv"])
-    if fid != port.F_ALT_BN128_FQ2:
+    if fid not in port.FQ2_FIELDS:
         plain = port.field_op(fid, port.OP_TO_PLAIN, a)
         np.testing.assert_array_equal(plain, golden[f"field/{name}/to_plain"])
         np.testing.assert_array_equal(port.field_op(fid, port.OP_FROM_PLAIN, plain), a)
 
 
-@pytest.mark.parametrize("fid", range(6))
+@pytest.mark.parametrize("fid", sorted(PRIME_FIELDS))
 def test_pymodel_field_matches_reference(golden, fid):
     name = FIELD_NAMES[fid]
-    f = [pm.ALT_BN128_Q, pm.ALT_BN128_R, pm.BLS12_377_Q, pm.BLS12_377_R, pm.BW6_761_Q,
-         pm.BW6_761_R][fid]
+    f = PRIME_FIELDS[fid]
 
     def dec(rows):
         return [f.from_mont(sum(int(r[j]) << (64 * j) for j in range(f.limbs64))) for r in rows]
@@ -117,12 +118,12 @@ def test_field_get_digit_reference_kats():
     assert [pm.get_digit(v, 12, 21 - i) for i in range(22)] == hex12
 
 
-@pytest.mark.parametrize("fid", [port.F_ALT_BN128_FR, port.F_BLS12_377_FR, port.F_BW6_761_FR])
+@pytest.mark.parametrize("fid", [port.F_ALT_BN128_FR, port.F_BLS12_377_FR, port.F_BW6_761_FR,
+                                 port.F_BLS12_381_FR])
 def test_signed_digits(golden, fid):
     """field_get_signed_digit / field_get_num_signed_digits (field_utils.tcc:102-239) and the
     recomposition property of do_test_signed_digits (test_fields.cpp:348-398)."""
-    f = {port.F_ALT_BN128_FR: pm.ALT_BN128_R, port.F_BLS12_377_FR: pm.BLS12_377_R,
-         port.F_BW6_761_FR: pm.BW6_761_R}[fid]
+    f = PRIME_FIELDS[fid]
     sc = golden[f"digits/{fid}/scalars"]
     plain = [f.from_mont(sum(int(r[j]) << (64 * j) for j in range(f.limbs64))) for r in sc]
     for c in (2, 3, 5, 8, 13, 16, 17, 20, 21):
@@ -267,7 +268,7 @@ def test_edge_case1_vectors(golden):
 def test_port_batch_to_special_and_batch_exp(golden, gid):
     np.testing.assert_array_equal(port.batch_to_special(gid, golden[f"to_special/{gid}/in"]),
                                   golden[f"to_special/{gid}/out"])
-    bits, window = {0: 254, 1: 254, 2: 253, 3: 377}[gid], 4
+    bits, window = pm.GROUPS[gid].fr.bits, 4
     _, one = port.group_constants(gid)
     table = port.window_table(gid, bits, window, one)
     assert table.shape[0] == (bits + window - 1) // window
@@ -289,7 +290,7 @@ def test_port_batch_to_special_and_batch_exp(golden, gid):
 @pytest.mark.parametrize("gid", GROUPS)
 def test_port_equals_live_reference(live_ref, gid):
     ref = live_ref
-    n = {0: 3000, 1: 700, 2: 1200, 3: 300}[gid]
+    n = {0: 3000, 1: 700, 2: 1200, 3: 300, 4: 300, 5: 300, 6: 1200, 7: 300}[gid]
     bases = ref.gen_bases_walk(gid, n, start=123)
     scalars = ref.gen_scalars(gid, n, start=999)
     np.testing.assert_array_equal(port.gen_bases_walk(gid, n, start=123), bases)
@@ -327,4 +328,4 @@ def test_wire_format_model_matches_reference_serializer(golden, gid):
     assert pts[2] is None and pm.wire_point(g, None) == want[2 * len(want) // 4:3 * len(want) // 4]
     sc = g.decode_scalars(golden[f"wire/{gid}/scalars"])
     assert b"".join(pm.wire_scalar(g, s) for s in sc) == golden[f"wire/{gid}/scalar_bytes"].tobytes()
-    assert len(want) // 4 == {0: 64, 1: 128, 2: 96, 3: 192}[gid]  # ffi/ffi.h:13-17,55-59 sizes
+    assert len(want) // 4 == {0: 64, 1: 128, 2: 96, 3: 192, 4: 192, 5: 192, 6: 96, 7: 192}[gid]  # ffi/ffi.h:13-17,55-59 sizes

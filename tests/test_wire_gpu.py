@@ -7,7 +7,7 @@ import pytest
 from oracle import pymodel as pm
 
 pytestmark = pytest.mark.gpu
-GROUPS = [0, 1, 2, 3]
+GROUPS = [0, 1, 2, 3, 4, 5, 6, 7]
 
 
 @pytest.mark.parametrize("gid", GROUPS)
@@ -70,7 +70,7 @@ def test_wire_rejects_what_the_reference_rejects(engine, ref, gid):
         engine.multi_exp_wire(gid, bytes(off), bytes(sw), engine.WIRE_CHECK_CURVE)
     # on the curve but outside the prime-order subgroup (is_in_safe_subgroup); alt_bn128 G1 has
     # cofactor 1, so every curve point passes there
-    if gid in (2, 3):
+    if gid in (2, 3, 5, 6):  # prime coordinate field and cofactor > 1
         b = g.b
         x = 5
         while True:
