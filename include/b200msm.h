@@ -138,6 +138,11 @@ bool b200msm_set_option(const char *name, int64_t value);
  * (first round), 5 carry rounds, 6 bucket reduction, 7 window reduction + final, 8 total. */
 size_t b200msm_last_timings(float *ms, size_t cap);
 const char *b200msm_timing_name(size_t phase);
+/* Device-side stopwatch for benchmarks: CUDA events recorded on the engine's own stream (the
+ * stream every kernel and copy of this library is issued on).  timer_stop waits for the stop
+ * event and returns the elapsed milliseconds between the two records, or a negative value. */
+bool b200msm_timer_start(void);
+float b200msm_timer_stop(void);
 /* number of kernel launches issued by this library since init */
 uint64_t b200msm_launch_count(void);
 /* window bits the engine picks for n points of a group */

@@ -30,6 +30,7 @@ __all__ = [
     "FORM_NORMAL", "FORM_SPECIAL", "B200MsmError", "lib_path", "load", "init", "shutdown",
     "group_bytes", "scalar_bytes", "multi_exp", "batch_exp", "batch_to_special", "group_sum",
     "ResidentBases", "ResidentScalars", "multi_exp_resident", "last_timings", "launch_count",
+    "timer_start", "timer_stop",
     "set_option", "window_bits", "shard_range", "multi_exp_wire", "wire_point_bytes",
     "WIRE_CHECK_CURVE", "WIRE_CHECK_SUBGROUP",
 ]
@@ -47,7 +48,8 @@ ABI_SYMBOLS = [
     "b200msm_scalars_upload", "b200msm_multi_exp_resident", "b200msm_release", "b200msm_sum",
     "b200msm_batch_to_special", "b200msm_batch_exp", "b200msm_debug_op", "b200msm_set_option",
     "b200msm_last_timings", "b200msm_timing_name", "b200msm_launch_count", "b200msm_window_bits",
-    "b200msm_wire_point_bytes", "b200msm_multi_exp_wire",
+    "b200msm_wire_point_bytes", "b200msm_multi_exp_wire", "b200msm_timer_start",
+    "b200msm_timer_stop",
 ]
 
 
@@ -98,6 +100,8 @@ def load():
         "b200msm_window_bits": (u32, [u32, sz]),
         "b200msm_wire_point_bytes": (sz, [u32]),
         "b200msm_multi_exp_wire": (C.c_bool, [u32, vp, sz, vp, sz, sz, u32, vp, sz]),
+        "b200msm_timer_start": (C.c_bool, []),
+        "b200msm_timer_stop": (C.c_float, []),
     }
     for name, (res, args) in sigs.items():
         f = getattr(L, name)
@@ -359,6 +363,21 @@ def last_timings() -> dict:
 
 def launch_count() -> int:
     return int(load().b200msm_launch_count())
+
+
+def timer_start() -> None:
+    """Records a CUDA event on the engine's stream (device-side stopwatch for benchmarks)."""
+    _ensure_init()
+    if not load().b200msm_timer_start():
+        _fail("timer_start")
+
+
+def timer_stop() -> float:
+    """Milliseconds on the device between timer_start() and now (waits for the stream)."""
+    ms = float(load().b200msm_timer_stop())
+    if ms < 0:
+        _fail("timer_stop")
+    return ms
 
 
 def set_option(name: str, value: int) -> None:

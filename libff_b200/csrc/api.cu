@@ -146,8 +146,28 @@ bool run_msm(Ctx &ctx, const GroupOps *ops, const void *d_aff, const uint8_t *d_
 size_t pick_parts(const Ctx &ctx, size_t n) {
     if (ctx.opt_h2d_parts > 0) return std::min<size_t>((size_t)ctx.opt_h2d_parts, std::max<size_t>(n, 1));
     if (n < ((size_t)1 << 21)) return 1;
-    if (n < ((size_t)1 << 23)) return 2;
-    return 3;
+    if (n < ((size_t)1 << 22)) return 2;
+    if (n < ((size_t)1 << 23)) return 3;
+    return 5;
+}
+
+// Range boundaries of a pipelined call: sizes grow geometrically (x h2d_growth %, default 1.3),
+// so the first upload -- the only one nothing overlaps -- is short, while the later, longer MSMs
+// still finish after their successor's upload.  bounds has parts + 1 entries.
+void pick_bounds(const Ctx &ctx, size_t n, size_t parts, size_t *bounds) {
+    const double g = ctx.opt_h2d_growth > 0 ? ctx.opt_h2d_growth / 100.0 : 1.3;
+    double total = 0, w = 1;
+    for (size_t k = 0; k < parts; k++, w *= g) total += w;
+    double acc = 0;
+    w = 1;
+    bounds[0] = 0;
+    for (size_t k = 0; k + 1 < parts; k++, w *= g) {
+        acc += w;
+        size_t b = (size_t)((double)n * (acc / total));
+        if (n >= ((size_t)1 << 16)) b &= ~(size_t)255;  // 16-byte aligned ranges in all arrays
+        bounds[k + 1] = std::min(std::max(b, bounds[k]), n);
+    }
+    bounds[parts] = n;
 }
 
 // ---- host -> device uploads ------------------------------------------------------------------
@@ -268,6 +288,12 @@ bool b200msm_init(int device) {
     for (auto &e : ctx->ev) B200_CUDA(cudaEventCreate(&e));
     for (auto &e : ctx->ev_copy) B200_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     B200_CUDA(cudaEventCreateWithFlags(&ctx->ev_sync, cudaEventDisableTiming));
+    int prio_lo = 0, prio_hi = 0;
+    B200_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    B200_CUDA(cudaStreamCreateWithPriority(&ctx->tail_stream, cudaStreamNonBlocking, prio_hi));
+    for (auto &e : ctx->ev_timer) B200_CUDA(cudaEventCreate(&e));
+    B200_CUDA(cudaEventCreateWithFlags(&ctx->ev_tail_go, cudaEventDisableTiming));
+    B200_CUDA(cudaEventCreateWithFlags(&ctx->ev_tail_done, cudaEventDisableTiming));
     g_ctx = ctx;
     return true;
 }
@@ -287,6 +313,10 @@ void b200msm_shutdown(void) {
     for (auto &e : g_ctx->ev) cudaEventDestroy(e);
     for (auto &e : g_ctx->ev_copy) cudaEventDestroy(e);
     cudaEventDestroy(g_ctx->ev_sync);
+    for (auto &e : g_ctx->ev_timer) cudaEventDestroy(e);
+    cudaEventDestroy(g_ctx->ev_tail_go);
+    cudaEventDestroy(g_ctx->ev_tail_done);
+    cudaStreamDestroy(g_ctx->tail_stream);
     cudaStreamDestroy(g_ctx->copy_stream);
     cudaStreamDestroy(g_ctx->stream);
     delete g_ctx;
@@ -337,9 +367,10 @@ bool b200msm_multi_exp(uint32_t group, const void *bases, size_t bases_bytes, co
     }
     // ---- pipelined: upload of range k + 1 (copy stream) under the MSM of range k
     const size_t gb = ops->group_bytes, sb = ops->scalar_bytes, ab = ops->affine_bytes;
-    const size_t one = n / parts;
-    auto lo_of = [&](size_t k) { return k * one; };
-    auto hi_of = [&](size_t k) { return k + 1 == parts ? n : (k + 1) * one; };
+    size_t bounds[MAX_H2D_PARTS + 1];
+    pick_bounds(ctx, n, parts, bounds);
+    auto lo_of = [&](size_t k) { return bounds[k]; };
+    auto hi_of = [&](size_t k) { return bounds[k + 1]; };
     // the compute stream must not overwrite the staging buffers of a previous call that is
     // still in flight: the copy stream starts after everything queued so far
     B200_CUDA(cudaEventRecord(ctx.ev_sync, ctx.stream));
@@ -365,6 +396,15 @@ bool b200msm_multi_exp(uint32_t group, const void *bases, size_t bases_bytes, co
         }
     });
     if (!mark_all(ctx, PH_INGEST + 1)) return false;
+    // the latency-bound tail of range k runs under the kernels of range k + 1
+    struct TailScope {
+        Ctx &c;
+        explicit TailScope(Ctx &c_) : c(c_) { c.defer_tail = true, c.tail_pending = false; }
+        ~TailScope() {
+            if (c.tail_pending) cudaStreamSynchronize(c.tail_stream);  // error paths
+            c.defer_tail = c.tail_pending = false;
+        }
+    } tail_scope(ctx);
     for (size_t k = 0; k < parts; k++) {
         const size_t lo = lo_of(k), cnt = hi_of(k) - lo;
         up.wait_for((int)k);
@@ -377,6 +417,10 @@ bool b200msm_multi_exp(uint32_t group, const void *bases, size_t bases_bytes, co
         if (!ops->msm(ctx, (char *)d_aff + lo * ab, (const uint8_t *)d_inf + lo, (char *)d_sc + lo * sb,
                       cnt, (char *)d_parts + k * gb))
             return false;
+    }
+    if (ctx.tail_pending) {
+        B200_CUDA(cudaStreamWaitEvent(ctx.stream, ctx.ev_tail_done, 0));
+        ctx.tail_pending = false;
     }
     if (!ops->sum(ctx, d_parts, parts, d_out)) return false;
     return finish_msm(ctx, ops, d_out, out);
@@ -604,6 +648,10 @@ bool b200msm_set_option(const char *name, int64_t value) {
     if (name && !strcmp(name, "window_bits")) return g_ctx->opt_window_bits = (int)value, true;
     if (name && !strcmp(name, "segment")) return g_ctx->opt_segment = (int)value, true;
     if (name && !strcmp(name, "reduce_chunk")) return g_ctx->opt_reduce_chunk = (int)value, true;
+    if (name && !strcmp(name, "h2d_growth")) {
+        if (value < 0 || value > 400) return set_error("h2d_growth out of range (percent)"), false;
+        return g_ctx->opt_h2d_growth = (int)value, true;
+    }
     if (name && !strcmp(name, "h2d_parts")) {
         if (value < 0 || value > MAX_H2D_PARTS) return set_error("h2d_parts out of range"), false;
         return g_ctx->opt_h2d_parts = (int)value, true;
@@ -622,6 +670,26 @@ const char *b200msm_timing_name(size_t phase) {
     static const char *names[PH_COUNT] = {"ingest", "digits", "scan", "scatter", "accumulate",
                                           "carry_rounds", "bucket_reduce", "final", "total"};
     return phase < (size_t)PH_COUNT ? names[phase] : "";
+}
+
+bool b200msm_timer_start(void) {
+    std::lock_guard<std::mutex> lk(g_mutex);
+    if (!ready()) return false;
+    B200_CUDA(cudaEventRecord(g_ctx->ev_timer[0], g_ctx->stream));
+    return true;
+}
+
+float b200msm_timer_stop(void) {
+    std::lock_guard<std::mutex> lk(g_mutex);
+    if (!g_ctx || cudaSetDevice(g_ctx->device) != cudaSuccess) return -1.0f;
+    float ms = -1.0f;
+    if (cudaEventRecord(g_ctx->ev_timer[1], g_ctx->stream) != cudaSuccess ||
+        cudaEventSynchronize(g_ctx->ev_timer[1]) != cudaSuccess ||
+        cudaEventElapsedTime(&ms, g_ctx->ev_timer[0], g_ctx->ev_timer[1]) != cudaSuccess) {
+        set_error("timer_stop: %s", cudaGetErrorString(cudaGetLastError()));
+        return -1.0f;
+    }
+    return ms;
 }
 
 uint64_t b200msm_launch_count(void) {

@@ -80,15 +80,24 @@ struct Ctx {
     cudaStream_t copy_stream = nullptr;          // host -> device uploads of a pipelined call
     cudaEvent_t ev_copy[MAX_H2D_PARTS] = {};     // "range k is on the device"
     cudaEvent_t ev_sync = nullptr;
+    // The last two kernels of an MSM (per-window totals, Horner) are one block per window and one
+    // warp: latency-bound.  In a pipelined host call they run on a high-priority side stream
+    // under the next range's digit/scatter/accumulation kernels.
+    cudaStream_t tail_stream = nullptr;
+    cudaEvent_t ev_tail_go = nullptr, ev_tail_done = nullptr;
+    bool defer_tail = false;    // set by the pipelined caller
+    bool tail_pending = false;  // a deferred tail may still be reading the reduction scratch
     void *slot_ptr[SL_COUNT] = {};
     size_t slot_bytes[SL_COUNT] = {};
     cudaEvent_t ev[PH_COUNT + 1] = {};
+    cudaEvent_t ev_timer[2] = {};                // b200msm_timer_start / _stop
     float last_ms[PH_COUNT] = {};
     bool have_timings = false;
     uint64_t launches = 0;
     int opt_window_bits = 0;  // 0 = automatic
     int opt_segment = 0;      // 0 = default
     int opt_h2d_parts = 0;    // 0 = automatic
+    int opt_h2d_growth = 0;   // size ratio of consecutive ranges in percent; 0 = default (130)
     int opt_reduce_chunk = 0; // log2 of the buckets per thread in the reduction; 0 = automatic
 
     bool reserve(Slot s, size_t bytes, void **out);

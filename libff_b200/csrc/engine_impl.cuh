@@ -249,6 +249,10 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
     if (!reserve_as(ctx, SL_CHUNKS, (size_t)Wu * nchunks * R::XW * 4, &chunks)) return false;
     if (!reserve_as(ctx, SL_CHUNK_TOTALS, (size_t)Wu * nchunks * R::XW * 4, &chunk_T)) return false;
     if (!reserve_as(ctx, SL_WINDOWS, (size_t)Wu * R::XW * 4, &windows)) return false;
+    if (ctx.tail_pending) {  // the previous range's tail reads chunks / chunk_T / windows
+        B200_CUDA(cudaStreamWaitEvent(st, ctx.ev_tail_done, 0));
+        ctx.tail_pending = false;
+    }
     k_bucket_reduce<C><<<dim3(cdiv(nchunks, 64), Wu), 64, 0, st>>>(buckets, hist, B, K, chunks, chunk_T);
     B200_LAUNCH_CHECK(ctx);
     B200_CUDA(cudaEventRecord(ctx.ev[PH_BUCKET_REDUCE + 1], st));
@@ -260,11 +264,21 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wr_smem));
         attr_set = true;
     }
-    k_window_reduce<C, WR_THREADS><<<Wu, WR_THREADS, wr_smem, st>>>(chunks, chunk_T, nchunks, log2K,
+    cudaStream_t ts = st;
+    if (ctx.defer_tail) {
+        ts = ctx.tail_stream;
+        B200_CUDA(cudaEventRecord(ctx.ev_tail_go, st));
+        B200_CUDA(cudaStreamWaitEvent(ts, ctx.ev_tail_go, 0));
+    }
+    k_window_reduce<C, WR_THREADS><<<Wu, WR_THREADS, wr_smem, ts>>>(chunks, chunk_T, nchunks, log2K,
                                                                    windows);
     B200_LAUNCH_CHECK(ctx);
-    k_final<C><<<1, 32, 0, st>>>(windows, Wu, c, (uint32_t *)d_out);
+    k_final<C><<<1, 32, 0, ts>>>(windows, Wu, c, (uint32_t *)d_out);
     B200_LAUNCH_CHECK(ctx);
+    if (ctx.defer_tail) {
+        B200_CUDA(cudaEventRecord(ctx.ev_tail_done, ts));
+        ctx.tail_pending = true;
+    }
     B200_CUDA(cudaEventRecord(ctx.ev[PH_FINAL + 1], st));
     return true;
 }

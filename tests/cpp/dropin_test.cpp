@@ -7,6 +7,7 @@
 // so the binary is not tracked); run on the GPU box by tests/test_dropin_gpu.py.
 #include <libff/algebra/curves/alt_bn128/alt_bn128_pp.hpp>
 #include <libff/algebra/curves/bls12_377/bls12_377_pp.hpp>
+#include <libff/algebra/curves/bls12_381/bls12_381_pp.hpp>
 #include <libff/algebra/curves/bw6_761/bw6_761_pp.hpp>
 #include <libff/algebra/scalar_multiplication/multiexp.hpp>
 #include <libff/common/rng.hpp>
@@ -209,6 +210,7 @@ int main()
     alt_bn128_pp::init_public_params();
     bls12_377_pp::init_public_params();
     bw6_761_pp::init_public_params();
+    bls12_381_pp::init_public_params();
     try {
         test_multi_exp_group_method<alt_bn128_G1, multi_exp_method_BDLO12>();
         test_multi_exp_group_method<alt_bn128_G1, multi_exp_method_BDLO12_signed>();
@@ -226,6 +228,21 @@ int main()
         test_batch_exp<alt_bn128_G2>(60, 4);
         test_batch_exp<bls12_377_G1>(100, 5);
         test_batch_exp<bw6_761_G1>(40, 4);
+        // the remaining groups (test_multiexp.cpp:322-326 runs bls12_381)
+        test_multi_exp_group_method<bls12_381_G1, multi_exp_method_BDLO12>();
+        test_multi_exp_group_method<bls12_381_G1, multi_exp_method_BDLO12_signed>();
+        test_multi_exp_group_method<bls12_381_G2, multi_exp_method_BDLO12>();
+        test_multi_exp_group_method<bls12_381_G2, multi_exp_method_BDLO12_signed>();
+        test_multi_exp_group_method<bls12_377_G2, multi_exp_method_BDLO12_signed>();
+        test_multi_exp_group_method<bw6_761_G2, multi_exp_method_BDLO12_signed>();
+        test_random<bls12_381_G1>(500);
+        test_random<bls12_381_G2>(200);
+        test_random<bls12_377_G2>(200);
+        test_random<bw6_761_G2>(100);
+        test_batch_exp<bls12_381_G1>(100, 5);
+        test_batch_exp<bls12_381_G2>(40, 4);
+        test_batch_exp<bls12_377_G2>(40, 4);
+        test_batch_exp<bw6_761_G2>(30, 4);
         test_edge_case1();
     } catch (const std::exception &e) {
         printf("EXCEPTION %s\n", e.what());
