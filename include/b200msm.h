@@ -127,6 +127,47 @@ bool b200msm_batch_exp(uint32_t group, size_t scalar_bits, size_t window,
 bool b200msm_debug_op(uint32_t group, uint32_t op, const void *a, const void *b, void *out,
                       size_t bytes, size_t n);
 
+/* ---- Precomputed multiples: multi_exp_stream_with_precompute (multiexp_stream.hpp:27-41,
+ * multiexp_stream.tcc:124-162, 195-223).  For every base P_i the table holds the W multiples
+ * P_i, 2^c P_i, ..., 2^((W-1) c) P_i with W = (scalar bits + c - 1) / c (b200msm_precompute_digits),
+ * so all digits of all scalars feed ONE set of 2^(c-1) buckets.  The table stays resident in HBM
+ * (a fixed proving key) and is released with b200msm_release.
+ * precompute:          builds the table on the device from resident bases; c = 0 lets the
+ *                      engine choose (b200msm_precompute_window_bits).
+ * precomputed_upload:  takes the table in the order the reference's stream has it -- for each
+ *                      base its W multiples -- as n * W in-memory GroupT elements.
+ * multi_exp_precomputed: scalars either resident (scalars_handle != 0) or on the host
+ *                      (scalars_handle == 0: n * sizeof(Fr) bytes, Montgomery form).
+ * Where W c equals the scalar width the reference drops the carry out of the top signed digit
+ * (field_utils.tcc:205-239); here such scalars are folded to r - s, so the result is always
+ * the group element sum s_i P_i. */
+uint32_t b200msm_precompute_window_bits(uint32_t group, size_t n);
+size_t b200msm_precompute_digits(uint32_t group, uint32_t c);
+bool b200msm_precompute(uint32_t group, uint64_t bases_handle, uint32_t c, uint64_t *table_handle);
+bool b200msm_precomputed_upload(uint32_t group, const void *elements, size_t bytes, size_t n,
+                                uint32_t c, uint32_t base_form, uint64_t *table_handle);
+bool b200msm_multi_exp_precomputed(uint32_t group, uint64_t table_handle, uint64_t scalars_handle,
+                                   const void *scalars, size_t scalars_bytes, void *out,
+                                   size_t out_bytes);
+
+/* ---- Streamed bases: multi_exp_stream / multi_exp_stream_with_precompute
+ * (multiexp_stream.tcc:164-223).  The scalars are given up front, the bases arrive in chunks
+ * (what the reference reads from its std::istream through a FIFO); every chunk is uploaded,
+ * decoded and reduced on the device while the caller reads the next one.  `encoding`:
+ * in-memory GroupT elements (special form Z = 1, or any Z), or the bytes of the reference's
+ * uncompressed binary stream encoding (curve_serialization.tcc:79-101: big-endian X then Y,
+ * plain or Montgomery values, (0, 1) = zero), decoded on the device.  precompute_c != 0: every
+ * base comes as its W multiples (stream layout of multiexp_stream.hpp:30-36).
+ * push returns once the chunk has left the caller's buffer.  finish releases the stream. */
+#define B200MSM_STREAM_MEMORY_SPECIAL 0u
+#define B200MSM_STREAM_MEMORY_NORMAL 1u
+#define B200MSM_STREAM_BINARY_PLAIN 2u
+#define B200MSM_STREAM_BINARY_MONTGOMERY 3u
+bool b200msm_stream_begin(uint32_t group, const void *scalars, size_t scalars_bytes, size_t n,
+                          uint32_t encoding, uint32_t precompute_c, uint64_t *stream);
+bool b200msm_stream_push(uint64_t stream, const void *elements, size_t bytes, size_t count);
+bool b200msm_stream_finish(uint64_t stream, void *out, size_t out_bytes);
+
 /* Tuning and measurement (not part of the reference surface).
  * option: "window_bits" (0 = automatic), "segment" (entries per thread of the accumulation),
  * "h2d_parts" (point ranges a host-buffer multi_exp is cut into so that uploads overlap the

@@ -30,7 +30,9 @@ __all__ = [
     "FORM_NORMAL", "FORM_SPECIAL", "B200MsmError", "lib_path", "load", "init", "shutdown",
     "group_bytes", "scalar_bytes", "multi_exp", "batch_exp", "batch_to_special", "group_sum",
     "ResidentBases", "ResidentScalars", "multi_exp_resident", "last_timings", "launch_count",
-    "timer_start", "timer_stop",
+    "timer_start", "timer_stop", "PrecomputedBases", "multi_exp_precomputed", "precompute_digits",
+    "precompute_window_bits", "MsmStream", "STREAM_MEMORY_SPECIAL", "STREAM_MEMORY_NORMAL",
+    "STREAM_BINARY_PLAIN", "STREAM_BINARY_MONTGOMERY",
     "set_option", "window_bits", "shard_range", "multi_exp_wire", "wire_point_bytes",
     "WIRE_CHECK_CURVE", "WIRE_CHECK_SUBGROUP",
 ]
@@ -49,7 +51,9 @@ ABI_SYMBOLS = [
     "b200msm_batch_to_special", "b200msm_batch_exp", "b200msm_debug_op", "b200msm_set_option",
     "b200msm_last_timings", "b200msm_timing_name", "b200msm_launch_count", "b200msm_window_bits",
     "b200msm_wire_point_bytes", "b200msm_multi_exp_wire", "b200msm_timer_start",
-    "b200msm_timer_stop",
+    "b200msm_timer_stop", "b200msm_precompute_window_bits", "b200msm_precompute_digits",
+    "b200msm_precompute", "b200msm_precomputed_upload", "b200msm_multi_exp_precomputed",
+    "b200msm_stream_begin", "b200msm_stream_push", "b200msm_stream_finish",
 ]
 
 
@@ -100,6 +104,14 @@ def load():
         "b200msm_window_bits": (u32, [u32, sz]),
         "b200msm_wire_point_bytes": (sz, [u32]),
         "b200msm_multi_exp_wire": (C.c_bool, [u32, vp, sz, vp, sz, sz, u32, vp, sz]),
+        "b200msm_precompute_window_bits": (u32, [u32, sz]),
+        "b200msm_precompute_digits": (sz, [u32, u32]),
+        "b200msm_precompute": (C.c_bool, [u32, u64, u32, C.POINTER(u64)]),
+        "b200msm_precomputed_upload": (C.c_bool, [u32, vp, sz, sz, u32, u32, C.POINTER(u64)]),
+        "b200msm_multi_exp_precomputed": (C.c_bool, [u32, u64, u64, vp, sz, vp, sz]),
+        "b200msm_stream_begin": (C.c_bool, [u32, vp, sz, sz, u32, u32, C.POINTER(u64)]),
+        "b200msm_stream_push": (C.c_bool, [u64, vp, sz, sz]),
+        "b200msm_stream_finish": (C.c_bool, [u64, vp, sz]),
         "b200msm_timer_start": (C.c_bool, []),
         "b200msm_timer_stop": (C.c_float, []),
     }
@@ -351,6 +363,111 @@ def multi_exp_resident(bases: ResidentBases, scalars: ResidentScalars, first: in
                                              _ptr(out), out.nbytes):
         _fail("b200msm_multi_exp_resident")
     return out
+
+
+# ---- precomputed multiples (multi_exp_stream_with_precompute, multiexp_stream.hpp:27-41) ---------
+
+def precompute_window_bits(group: int, n: int) -> int:
+    return int(load().b200msm_precompute_window_bits(group, n))
+
+
+def precompute_digits(group: int, c: int) -> int:
+    """multiples per base for digit size c: (Fr::num_bits + c - 1) / c (multiexp_stream.tcc:205)"""
+    return int(load().b200msm_precompute_digits(group, c))
+
+
+class PrecomputedBases(_Resident):
+    """Table of the multiples 2^(k c) P_i kept in HBM.  Either built on the device from resident
+    bases (`bases=`), or uploaded in the order of the reference's precompute stream (`elements=`:
+    n * digits in-memory elements, for each base its multiples)."""
+
+    def __init__(self, group: int, bases: Optional[ResidentBases] = None, c: int = 0,
+                 elements=None, base_form: int = FORM_SPECIAL):
+        _ensure_init()
+        h = C.c_uint64(0)
+        if bases is not None:
+            if not load().b200msm_precompute(group, bases.handle, c, C.byref(h)):
+                _fail("b200msm_precompute")
+            n = bases.n
+            self.c = c or precompute_window_bits(group, n)
+        else:
+            e = _as_u64(elements, "elements")
+            per = precompute_digits(group, c)
+            total = _count(e, group_bytes(group), "elements")
+            if per == 0 or total % per:
+                raise B200MsmError(f"elements: {total} is not a multiple of {per} digits")
+            n = total // per
+            if not load().b200msm_precomputed_upload(group, _ptr(e), e.nbytes, n, c, base_form,
+                                                     C.byref(h)):
+                _fail("b200msm_precomputed_upload")
+            self.c = c
+        super().__init__(h.value, group, n)
+
+
+def multi_exp_precomputed(table: PrecomputedBases, scalars) -> np.ndarray:
+    """sum s_i P_i from the table; `scalars` is a ResidentScalars or a host array of n scalars."""
+    group = table.group
+    out = np.zeros(group_bytes(group) // 8, dtype=np.uint64)
+    if isinstance(scalars, ResidentScalars):
+        ok = load().b200msm_multi_exp_precomputed(group, table.handle, scalars.handle, None, 0,
+                                                  _ptr(out), out.nbytes)
+    else:
+        s = _as_u64(scalars, "scalars")
+        ok = load().b200msm_multi_exp_precomputed(group, table.handle, 0, _ptr(s), s.nbytes,
+                                                  _ptr(out), out.nbytes)
+    if not ok:
+        _fail("b200msm_multi_exp_precomputed")
+    return out
+
+
+# ---- streamed bases (multi_exp_stream, multiexp_stream.tcc:164-193) ------------------------------
+STREAM_MEMORY_SPECIAL, STREAM_MEMORY_NORMAL, STREAM_BINARY_PLAIN, STREAM_BINARY_MONTGOMERY = 0, 1, 2, 3
+
+
+class MsmStream:
+    """The scalars are known up front, the bases arrive in chunks (`push`), `finish` returns the sum.
+    encoding: in-memory elements, or the bytes of the reference's uncompressed binary stream
+    encoding (decoded on the device).  precompute_c != 0: every base comes as its multiples."""
+
+    def __init__(self, group: int, scalars, encoding: int = STREAM_MEMORY_SPECIAL,
+                 precompute_c: int = 0):
+        _ensure_init()
+        s = _as_u64(scalars, "scalars")
+        self.group, self.n = group, _count(s, scalar_bytes(group), "scalars")
+        self.encoding, self.c = encoding, precompute_c
+        h = C.c_uint64(0)
+        if not load().b200msm_stream_begin(group, _ptr(s), s.nbytes, self.n, encoding, precompute_c,
+                                           C.byref(h)):
+            _fail("b200msm_stream_begin")
+        self.handle = h.value
+
+    def push(self, elements, count: Optional[int] = None) -> None:
+        if isinstance(elements, (bytes, bytearray, memoryview)):
+            buf = np.frombuffer(elements, dtype=np.uint8)
+        else:
+            buf = np.ascontiguousarray(elements)
+        if count is None:
+            per = precompute_digits(self.group, self.c) if self.c else 1
+            eb = group_bytes(self.group) if self.encoding <= STREAM_MEMORY_NORMAL \
+                else wire_point_bytes(self.group)
+            count = buf.nbytes // (eb * per)
+        if not load().b200msm_stream_push(self.handle, buf.ctypes.data_as(C.c_void_p), buf.nbytes, count):
+            _fail("b200msm_stream_push")
+
+    def finish(self) -> np.ndarray:
+        out = np.zeros(group_bytes(self.group) // 8, dtype=np.uint64)
+        h, self.handle = self.handle, 0
+        if not load().b200msm_stream_finish(h, _ptr(out), out.nbytes):
+            _fail("b200msm_stream_finish")
+        return out
+
+    def __del__(self):
+        try:
+            if self.handle and _lib is not None:
+                tmp = np.zeros(group_bytes(self.group) // 8, dtype=np.uint64)
+                _lib.b200msm_stream_finish(self.handle, _ptr(tmp), tmp.nbytes)
+        except Exception:
+            pass
 
 
 def last_timings() -> dict:

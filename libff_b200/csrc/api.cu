@@ -67,9 +67,24 @@ struct Resident {
     uint32_t group;
     bool is_bases;
     size_t n;
-    void *data = nullptr;   // affine bases or scalars
-    uint8_t *inf = nullptr; // bases only
+    void *data = nullptr;   // affine bases, scalars, or a table of precomputed multiples
+    uint8_t *inf = nullptr; // bases and tables
+    bool is_table = false;
+    MsmShape shape = {0, 0, 1, 0};  // tables only
 };
+
+// A streamed MSM in progress (b200msm_stream_*)
+struct Stream {
+    uint32_t group;
+    size_t n, consumed = 0;
+    uint32_t encoding, c;
+    int W;                    // elements per base in the stream (1 without precomputation)
+    void *d_scalars = nullptr;
+    void *d_partials = nullptr;
+    size_t partials = 0;
+};
+constexpr size_t STREAM_MAX_PARTIALS = 256;
+std::map<uint64_t, Stream> g_streams;
 
 std::mutex g_mutex;
 Ctx *g_ctx = nullptr;
@@ -132,11 +147,11 @@ bool finish_msm(Ctx &ctx, const GroupOps *ops, const void *d_out, void *out) {
 }
 
 bool run_msm(Ctx &ctx, const GroupOps *ops, const void *d_aff, const uint8_t *d_inf,
-             const void *d_scalars, size_t n, void *out) {
+             const void *d_scalars, size_t n, void *out, const MsmShape *shape = nullptr) {
     void *d_out;
     if (!ctx.reserve(SL_OUT, ops->group_bytes, &d_out)) return false;
     if (!mark_all(ctx, PH_INGEST + 1)) return false;
-    if (!ops->msm(ctx, d_aff, d_inf, d_scalars, n, d_out)) return false;
+    if (!ops->msm(ctx, d_aff, d_inf, d_scalars, n, d_out, shape)) return false;
     return finish_msm(ctx, ops, d_out, out);
 }
 
@@ -308,6 +323,12 @@ void b200msm_shutdown(void) {
         if (kv.second.inf) cudaFree(kv.second.inf);
     }
     g_resident.clear();
+    for (auto &kv : g_streams) {
+        cudaFree(kv.second.d_scalars);
+        cudaFree(kv.second.d_partials);
+    }
+    g_streams.clear();
+    cudaStreamSynchronize(g_ctx->tail_stream);
     g_ctx->release_all();
     g_stager.release();
     for (auto &e : g_ctx->ev) cudaEventDestroy(e);
@@ -399,7 +420,7 @@ bool b200msm_multi_exp(uint32_t group, const void *bases, size_t bases_bytes, co
     // the latency-bound tail of range k runs under the kernels of range k + 1
     struct TailScope {
         Ctx &c;
-        explicit TailScope(Ctx &c_) : c(c_) { c.defer_tail = true, c.tail_pending = false; }
+        explicit TailScope(Ctx &c_) : c(c_) { c.defer_tail = true; }
         ~TailScope() {
             if (c.tail_pending) cudaStreamSynchronize(c.tail_stream);  // error paths
             c.defer_tail = c.tail_pending = false;
@@ -415,7 +436,7 @@ bool b200msm_multi_exp(uint32_t group, const void *bases, size_t bases_bytes, co
             return false;
         B200_CUDA(cudaEventRecord(ctx.ev[PH_INGEST + 1], ctx.stream));
         if (!ops->msm(ctx, (char *)d_aff + lo * ab, (const uint8_t *)d_inf + lo, (char *)d_sc + lo * sb,
-                      cnt, (char *)d_parts + k * gb))
+                      cnt, (char *)d_parts + k * gb, nullptr))
             return false;
     }
     if (ctx.tail_pending) {
@@ -467,7 +488,7 @@ bool b200msm_multi_exp_wire(uint32_t group, const void *points, size_t points_by
                          err & 2 ? "point not on curve " : "", err & 4 ? "point not in subgroup" : ""),
                false;
     if (!mark_all(ctx, PH_INGEST + 1)) return false;
-    if (!ops->msm(ctx, d_aff, (const uint8_t *)d_inf, d_sc, n, d_out)) return false;
+    if (!ops->msm(ctx, d_aff, (const uint8_t *)d_inf, d_sc, n, d_out, nullptr)) return false;
     if (!ops->wire_encode(ctx, d_out, d_wire_out)) return false;
     std::vector<unsigned char> tmp(pb);
     B200_CUDA(cudaMemcpyAsync(tmp.data(), d_wire_out, pb, cudaMemcpyDeviceToHost, ctx.stream));
@@ -527,6 +548,7 @@ bool b200msm_multi_exp_resident(uint32_t group, uint64_t bases_handle, uint64_t 
     if (!ops || !ready()) return false;
     auto b = g_resident.find(bases_handle), s = g_resident.find(scalars_handle);
     if (b == g_resident.end() || s == g_resident.end() || !b->second.is_bases || s->second.is_bases ||
+        s->second.is_table ||
         b->second.group != group || s->second.group != group)
         return set_error("multi_exp_resident: bad handle"), false;
     if (first + n > b->second.n || first + n > s->second.n || out_bytes != ops->group_bytes || !out)
@@ -536,6 +558,272 @@ bool b200msm_multi_exp_resident(uint32_t group, uint64_t bases_handle, uint64_t 
     return run_msm(ctx, ops, (const char *)b->second.data + first * ops->affine_bytes,
                    b->second.inf + first, (const char *)s->second.data + first * ops->scalar_bytes, n,
                    out);
+}
+
+// ---- precomputed multiples (multi_exp_stream_with_precompute, multiexp_stream.hpp:27-41) -----
+
+uint32_t b200msm_precompute_window_bits(uint32_t group, size_t n) {
+    const GroupOps *ops = ops_for(group);
+    if (!ops) return 0;
+    // one bucket set for all digits: n * W * 10 + 2^(c-1) * 53 (see pick_window_bits)
+    double best = 0;
+    uint32_t best_c = 2;
+    for (uint32_t c = 2; c <= 24; c++) {
+        const double W = (double)((ops->scalar_bits + c - 1) / c);
+        if ((double)n * W >= 2147483648.0) continue;
+        const double cost = (double)n * W * 10.0 + (double)(1u << (c - 1)) * 53.0;
+        if (best == 0 || cost < best) best = cost, best_c = c;
+    }
+    return best_c;
+}
+
+size_t b200msm_precompute_digits(uint32_t group, uint32_t c) {
+    const GroupOps *ops = ops_for(group);
+    if (!ops || c < 2 || c > 24) return 0;
+    return (size_t)((ops->scalar_bits + (int)c - 1) / (int)c);  // multiexp_stream.tcc:205
+}
+
+bool b200msm_precompute(uint32_t group, uint64_t bases_handle, uint32_t c, uint64_t *table_handle) {
+    std::lock_guard<std::mutex> lk(g_mutex);
+    const GroupOps *ops = checked_ops(group);
+    if (!ops || !ready()) return false;
+    auto b = g_resident.find(bases_handle);
+    if (b == g_resident.end() || !b->second.is_bases || b->second.group != group || !table_handle)
+        return set_error("precompute: bad handle"), false;
+    const size_t n = b->second.n;
+    if (c == 0) c = b200msm_precompute_window_bits(group, n);
+    if (c < 2 || c > 24) return set_error("precompute: digit size %u outside [2, 24]", c), false;
+    const int W = (ops->scalar_bits + (int)c - 1) / (int)c;
+    if ((uint64_t)n * W >= (1ull << 31))
+        return set_error("precompute: n * digits = %llu exceeds 2^31 - 1 table entries",
+                         (unsigned long long)n * W), false;
+    Ctx &ctx = *g_ctx;
+    Resident r{group, false, n};
+    r.is_table = true;
+    r.shape = MsmShape{(int)c, W, 1u, (uint32_t)n};  // built window-major: table[w * n + i]
+    B200_CUDA(cudaMalloc(&r.data, (size_t)W * n * ops->affine_bytes));
+    B200_CUDA(cudaMalloc((void **)&r.inf, n));
+    bool ok = cudaMemcpyAsync(r.inf, b->second.inf, n, cudaMemcpyDeviceToDevice, ctx.stream) == cudaSuccess &&
+              ops->precompute(ctx, b->second.data, b->second.inf, n, (int)c, W, r.data);
+    if (ok && cudaStreamSynchronize(ctx.stream) != cudaSuccess) ok = false, set_error("precompute failed");
+    if (!ok) {
+        cudaFree(r.data);
+        cudaFree(r.inf);
+        return false;
+    }
+    *table_handle = g_next_handle++;
+    g_resident[*table_handle] = r;
+    return true;
+}
+
+bool b200msm_precomputed_upload(uint32_t group, const void *elements, size_t bytes, size_t n,
+                                uint32_t c, uint32_t base_form, uint64_t *table_handle) {
+    std::lock_guard<std::mutex> lk(g_mutex);
+    const GroupOps *ops = checked_ops(group);
+    if (!ops || !ready()) return false;
+    if (c < 2 || c > 24) return set_error("precomputed_upload: digit size %u outside [2, 24]", c), false;
+    if (base_form > 1) return set_error("invalid base_form %u", base_form), false;
+    const int W = (ops->scalar_bits + (int)c - 1) / (int)c;
+    const size_t entries = n * (size_t)W;
+    if (!table_handle || !elements || n == 0 || bytes != entries * ops->group_bytes)
+        return set_error("precomputed_upload: bad arguments (need n * %d elements)", W), false;
+    if (entries >= (1ull << 31)) return set_error("precomputed_upload: too many entries"), false;
+    Ctx &ctx = *g_ctx;
+    Resident r{group, false, n};
+    r.is_table = true;
+    r.shape = MsmShape{(int)c, W, (uint32_t)W, 1u};  // the reference's stream order: base-major
+    void *d_raw;
+    uint8_t *d_inf_all;
+    if (!ctx.reserve(SL_RAW, bytes, &d_raw)) return false;
+    if (!ctx.reserve(SL_TABLE_INF, entries, (void **)&d_inf_all)) return false;
+    B200_CUDA(cudaMalloc(&r.data, entries * ops->affine_bytes));
+    B200_CUDA(cudaMalloc((void **)&r.inf, n));
+    if (!g_stager.init()) return false;
+    bool ok = upload(ctx.device, d_raw, elements, bytes, ctx.stream) &&
+              ops->ingest(ctx, d_raw, entries, base_form, r.data, d_inf_all) &&
+              // a base is skipped when its first element is zero (all its multiples are)
+              cudaMemcpy2DAsync(r.inf, 1, d_inf_all, (size_t)W, 1, n, cudaMemcpyDeviceToDevice,
+                                ctx.stream) == cudaSuccess;
+    if (ok && cudaStreamSynchronize(ctx.stream) != cudaSuccess) ok = false, set_error("ingest failed");
+    if (!ok) {
+        cudaFree(r.data);
+        cudaFree(r.inf);
+        return false;
+    }
+    *table_handle = g_next_handle++;
+    g_resident[*table_handle] = r;
+    return true;
+}
+
+bool b200msm_multi_exp_precomputed(uint32_t group, uint64_t table_handle, uint64_t scalars_handle,
+                                   const void *scalars, size_t scalars_bytes, void *out,
+                                   size_t out_bytes) {
+    std::lock_guard<std::mutex> lk(g_mutex);
+    const GroupOps *ops = checked_ops(group);
+    if (!ops || !ready()) return false;
+    auto t = g_resident.find(table_handle);
+    if (t == g_resident.end() || !t->second.is_table || t->second.group != group)
+        return set_error("multi_exp_precomputed: bad table handle"), false;
+    const size_t n = t->second.n;
+    if (out_bytes != ops->group_bytes || !out) return set_error("multi_exp_precomputed: bad out"), false;
+    Ctx &ctx = *g_ctx;
+    const void *d_sc = nullptr;
+    B200_CUDA(cudaEventRecord(ctx.ev[0], ctx.stream));
+    if (scalars_handle != 0) {
+        auto sc = g_resident.find(scalars_handle);
+        if (sc == g_resident.end() || sc->second.is_bases || sc->second.is_table ||
+            sc->second.group != group || sc->second.n != n)
+            return set_error("multi_exp_precomputed: bad scalars handle"), false;
+        d_sc = sc->second.data;
+    } else {
+        if (!scalars || scalars_bytes != n * ops->scalar_bytes)
+            return set_error("multi_exp_precomputed: need %zu scalars", n), false;
+        void *d;
+        if (!ctx.reserve(SL_SCALARS, scalars_bytes, &d)) return false;
+        if (!g_stager.init()) return false;
+        if (!upload(ctx.device, d, scalars, scalars_bytes, ctx.stream))
+            return set_error("multi_exp_precomputed: host to device copy failed"), false;
+        d_sc = d;
+    }
+    return run_msm(ctx, ops, t->second.data, t->second.inf, d_sc, n, out, &t->second.shape);
+}
+
+// ---- streamed bases (multi_exp_stream / multi_exp_stream_with_precompute, multiexp_stream.tcc:
+// 164-223): the scalars are known up front, the bases arrive in chunks ------------------------
+
+static size_t stream_element_bytes(const GroupOps *ops, uint32_t encoding) {
+    return encoding <= B200MSM_STREAM_MEMORY_NORMAL ? ops->group_bytes : ops->affine_bytes;
+}
+
+bool b200msm_stream_begin(uint32_t group, const void *scalars, size_t scalars_bytes, size_t n,
+                          uint32_t encoding, uint32_t precompute_c, uint64_t *stream) {
+    std::lock_guard<std::mutex> lk(g_mutex);
+    const GroupOps *ops = checked_ops(group);
+    if (!ops || !ready()) return false;
+    if (encoding > B200MSM_STREAM_BINARY_MONTGOMERY)
+        return set_error("stream_begin: unknown encoding %u", encoding), false;
+    if (precompute_c != 0 && (precompute_c < 2 || precompute_c > 24))
+        return set_error("stream_begin: digit size %u outside [2, 24]", precompute_c), false;
+    if (!stream || scalars_bytes != n * ops->scalar_bytes || (n > 0 && !scalars))
+        return set_error("stream_begin: bad arguments"), false;
+    Ctx &ctx = *g_ctx;
+    Stream st{group, n};
+    st.encoding = encoding;
+    st.c = precompute_c;
+    st.W = precompute_c ? (ops->scalar_bits + (int)precompute_c - 1) / (int)precompute_c : 1;
+    B200_CUDA(cudaMalloc(&st.d_scalars, std::max<size_t>(scalars_bytes, 16)));
+    B200_CUDA(cudaMalloc(&st.d_partials, STREAM_MAX_PARTIALS * ops->group_bytes));
+    if (!g_stager.init()) return false;
+    if (n > 0 && (!upload(ctx.device, st.d_scalars, scalars, scalars_bytes, ctx.stream) ||
+                  cudaStreamSynchronize(ctx.stream) != cudaSuccess)) {
+        cudaFree(st.d_scalars);
+        cudaFree(st.d_partials);
+        return set_error("stream_begin: host to device copy failed"), false;
+    }
+    *stream = g_next_handle++;
+    g_streams[*stream] = st;
+    return true;
+}
+
+bool b200msm_stream_push(uint64_t stream, const void *elements, size_t bytes, size_t count) {
+    std::lock_guard<std::mutex> lk(g_mutex);
+    auto it = g_streams.find(stream);
+    if (it == g_streams.end()) return set_error("stream_push: unknown stream"), false;
+    if (!ready()) return false;
+    Stream &st = it->second;
+    const GroupOps *ops = ops_for(st.group);
+    const size_t eb = stream_element_bytes(ops, st.encoding);
+    const size_t entries = count * (size_t)st.W;
+    if (st.consumed + count > st.n)
+        return set_error("stream_push: %zu bases pushed, the stream holds %zu scalars",
+                         st.consumed + count, st.n), false;
+    if (bytes != entries * eb || (count > 0 && !elements))
+        return set_error("stream_push: %zu bytes for %zu x %d elements of %zu bytes", bytes, count,
+                         st.W, eb), false;
+    if (count == 0) return true;
+    if (entries >= (1ull << 31)) return set_error("stream_push: chunk too large"), false;
+    Ctx &ctx = *g_ctx;
+    void *d_in, *d_aff, *d_inf;
+    if (!ctx.reserve(st.encoding <= B200MSM_STREAM_MEMORY_NORMAL ? SL_RAW : SL_STREAM_IN, bytes, &d_in))
+        return false;
+    if (!ctx.reserve(SL_AFF, entries * ops->affine_bytes, &d_aff)) return false;
+    if (!ctx.reserve(SL_INF, entries, &d_inf)) return false;
+    if (st.partials == STREAM_MAX_PARTIALS) {  // fold the partial results into one
+        if (ctx.tail_pending) {
+            B200_CUDA(cudaStreamWaitEvent(ctx.stream, ctx.ev_tail_done, 0));
+            ctx.tail_pending = false;
+        }
+        void *d_tmp;
+        if (!ctx.reserve(SL_OUT, ops->group_bytes, &d_tmp)) return false;
+        if (!ops->sum(ctx, st.d_partials, st.partials, d_tmp)) return false;
+        B200_CUDA(cudaMemcpyAsync(st.d_partials, d_tmp, ops->group_bytes, cudaMemcpyDeviceToDevice,
+                                  ctx.stream));
+        st.partials = 1;
+    }
+    B200_CUDA(cudaEventRecord(ctx.ev[0], ctx.stream));
+    if (!upload(ctx.device, d_in, elements, bytes, ctx.stream))
+        return set_error("stream_push: host to device copy failed"), false;
+    if (st.encoding <= B200MSM_STREAM_MEMORY_NORMAL) {
+        if (!ops->ingest(ctx, d_in, entries, st.encoding == B200MSM_STREAM_MEMORY_SPECIAL ? 1u : 0u,
+                         d_aff, (uint8_t *)d_inf))
+            return false;
+    } else {
+        if (!ops->stream_decode(ctx, d_in, entries,
+                                st.encoding == B200MSM_STREAM_BINARY_MONTGOMERY ? 1u : 0u, d_aff,
+                                (uint8_t *)d_inf))
+            return false;
+    }
+    const uint8_t *d_base_inf = (const uint8_t *)d_inf;
+    if (st.W > 1) {  // per-base flag = flag of the base's first element
+        void *d_bi;
+        if (!ctx.reserve(SL_TABLE_INF, count, &d_bi)) return false;
+        B200_CUDA(cudaMemcpy2DAsync(d_bi, 1, d_inf, (size_t)st.W, 1, count, cudaMemcpyDeviceToDevice,
+                                    ctx.stream));
+        d_base_inf = (const uint8_t *)d_bi;
+    }
+    if (!mark_all(ctx, PH_INGEST + 1)) return false;
+    const MsmShape shape{(int)st.c, st.W, (uint32_t)st.W, 1u};
+    // the latency-bound tail of this chunk runs under the kernels of the next one
+    ctx.defer_tail = true;
+    const bool ok = ops->msm(ctx, d_aff, d_base_inf,
+                             (const char *)st.d_scalars + st.consumed * ops->scalar_bytes, count,
+                             (char *)st.d_partials + st.partials * ops->group_bytes,
+                             st.c ? &shape : nullptr);
+    ctx.defer_tail = false;
+    if (!ok) return false;
+    st.partials++;
+    st.consumed += count;
+    return true;
+}
+
+bool b200msm_stream_finish(uint64_t stream, void *out, size_t out_bytes) {
+    std::lock_guard<std::mutex> lk(g_mutex);
+    auto it = g_streams.find(stream);
+    if (it == g_streams.end()) return set_error("stream_finish: unknown stream"), false;
+    Stream st = it->second;
+    const GroupOps *ops = ops_for(st.group);
+    bool ok = ready();
+    if (ok && g_ctx->tail_pending) {
+        ok = cudaStreamWaitEvent(g_ctx->stream, g_ctx->ev_tail_done, 0) == cudaSuccess;
+        g_ctx->tail_pending = false;
+    }
+    if (ok && (out_bytes != ops->group_bytes || !out)) ok = false, set_error("stream_finish: bad out");
+    if (ok && st.consumed != st.n)
+        ok = false, set_error("stream_finish: %zu of %zu bases were pushed", st.consumed, st.n);
+    if (ok) {
+        Ctx &ctx = *g_ctx;
+        void *d_out;
+        ok = ctx.reserve(SL_OUT, ops->group_bytes, &d_out) &&
+             ops->sum(ctx, st.d_partials, st.partials, d_out) &&
+             cudaMemcpyAsync(out, d_out, ops->group_bytes, cudaMemcpyDeviceToHost, ctx.stream) == cudaSuccess &&
+             cudaStreamSynchronize(ctx.stream) == cudaSuccess;
+        if (!ok && g_error.empty()) set_error("stream_finish: device error");
+    }
+    if (g_ctx) cudaStreamSynchronize(g_ctx->stream);
+    cudaFree(st.d_scalars);
+    cudaFree(st.d_partials);
+    g_streams.erase(it);
+    return ok;
 }
 
 bool b200msm_release(uint64_t handle) {

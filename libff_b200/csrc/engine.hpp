@@ -69,6 +69,9 @@ enum Slot {
     SL_WIRE_IN,
     SL_WIRE_SC,
     SL_WIRE_MISC,
+    SL_PRE_STATE,   // XYZZ running multiples while a table is built
+    SL_PRE_RAW,     // the same in reference layout, input of the batch normalisation
+    SL_STREAM_IN,   // encoded chunk of a streamed MSM
     SL_COUNT
 };
 
@@ -112,6 +115,16 @@ inline bool reserve_as(Ctx &ctx, Slot s, size_t bytes, T **out) {
     return true;
 }
 
+// Shape of an MSM over a table of precomputed multiples 2^(w c) P_i (multiexp_stream.tcc:124-162):
+// the digit of window w of scalar i selects table[i * pstride + w * wstride], and every window
+// feeds the same 2^(c-1) buckets.  nullptr = the plain MSM (one bucket set per window).
+struct MsmShape {
+    int c;              // digit bits the table was built for
+    int W;              // digits per scalar = multiples per base = ceil(scalar bits / c)
+    uint32_t pstride;   // table index stride between bases
+    uint32_t wstride;   // table index stride between multiples of one base
+};
+
 // Type-erased per-group entry points, implemented once per group in group_*.cu.
 struct GroupOps {
     uint32_t id;
@@ -121,7 +134,14 @@ struct GroupOps {
     bool (*ingest)(Ctx &, const void *d_raw, size_t n, uint32_t form, void *d_aff, uint8_t *d_inf);
     // the MSM proper; result (reference layout) into d_out
     bool (*msm)(Ctx &, const void *d_aff, const uint8_t *d_inf, const void *d_scalars, size_t n,
-                void *d_out);
+                void *d_out, const MsmShape *shape);
+    // table[w * n + i] = 2^(w c) P_i (device affine), w < W, from n device-affine bases
+    bool (*precompute)(Ctx &, const void *d_aff, const uint8_t *d_inf, size_t n, int c, int W,
+                       void *d_table);
+    // libff's binary stream encoding (curve_serialization.tcc:79-101, uncompressed) -> device
+    // affine + infinity flags; flags bit 0: Montgomery form (else plain)
+    bool (*stream_decode)(Ctx &, const void *d_bytes, size_t n, uint32_t flags, void *d_aff,
+                          uint8_t *d_inf);
     bool (*sum)(Ctx &, const void *d_raw, size_t count, void *d_out);
     bool (*to_special)(Ctx &, void *d_raw, size_t n);
     bool (*batch_exp)(Ctx &, const void *d_table_raw, size_t rows, size_t row_len, int window,

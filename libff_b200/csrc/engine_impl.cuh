@@ -142,7 +142,7 @@ inline uint32_t pick_segment(const Ctx &ctx, size_t total) {
 
 template <class C>
 bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_scalars, size_t n,
-              void *d_out) {
+              void *d_out, const MsmShape *shape) {
     using R = Raw<C>;
     using F = typename C::Fq;
     cudaStream_t st = ctx.stream;
@@ -155,11 +155,15 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
         set_error("multi_exp: n = %zu exceeds the 2^31 - 1 points one device shard addresses", n);
         return false;
     }
-    const int c = (int)pick_window_bits<C>(ctx, n);
-    const int W = (C::Fr::Params::BITS + 1 + c - 1) / c;
+    const bool pre = shape != nullptr;
+    const int c = pre ? shape->c : (int)pick_window_bits<C>(ctx, n);
+    const int W = pre ? shape->W : (C::Fr::Params::BITS + 1 + c - 1) / c;
     const uint32_t B = 1u << (c - 1);
-    const size_t M = (size_t)W * B;
-    if ((uint64_t)n * W >= (1ull << 32)) {
+    const uint32_t bstride = pre ? 0u : B;         // precomputed multiples share one bucket set
+    const size_t M = pre ? (size_t)B : (size_t)W * B;
+    // W c == scalar bits: the top digit may carry out; k_digits folds such scalars to r - s
+    const int fold_bit = pre && W * c - 1 < C::Fr::Params::BITS ? W * c - 1 : -1;
+    if ((uint64_t)n * W >= (pre ? (1ull << 31) : (1ull << 32))) {
         set_error("multi_exp: n * windows = %llu does not fit 32-bit positions",
                   (unsigned long long)n * W);
         return false;
@@ -177,7 +181,7 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
     B200_CUDA(cudaMemsetAsync(hist, 0, M * 4, st));
     B200_CUDA(cudaMemsetAsync(offsets + M + 1, 0, 4, st));
     k_digits<C><<<cdiv(n, 256), 256, 0, st>>>((const uint32_t *)d_scalars, d_inf, digits, hist,
-                                               offsets + M + 1, (uint32_t)n, c, W);
+                                               offsets + M + 1, (uint32_t)n, c, W, bstride, fold_bit);
     B200_LAUNCH_CHECK(ctx);
     B200_CUDA(cudaEventRecord(ctx.ev[PH_DIGITS + 1], st));
     // --- offsets
@@ -196,7 +200,8 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
     B200_CUDA(cudaMemcpyAsync(meta, offsets + M, 8, cudaMemcpyDeviceToHost, st));
     B200_CUDA(cudaStreamSynchronize(st));
     const uint32_t total = meta[0];
-    const int Wu = std::max<int>(1, std::min<int>(W, (int)meta[1]));  // windows that hold items
+    // windows (bucket sets) that hold items
+    const int Wu = pre ? 1 : std::max<int>(1, std::min<int>(W, (int)meta[1]));
     const uint32_t seg = pick_segment(ctx, total);
     const size_t t1 = ((size_t)total + seg - 1) / seg;
     uint32_t *seg_bucket;
@@ -205,7 +210,9 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
     if (!reserve_as(ctx, SL_SORTED, ((size_t)W * n + 4) * sizeof(Entry), &sorted)) return false;
     // --- scatter
     k_scatter<C><<<dim3(cdiv(n, 256), W), 256, 0, st>>>(digits, cursor, sorted, seg_bucket,
-                                                       (uint32_t)n, c, seg);
+                                                       (uint32_t)n, seg, bstride,
+                                                       pre ? shape->pstride : 1u,
+                                                       pre ? shape->wstride : 0u);
     B200_LAUNCH_CHECK(ctx);
     B200_CUDA(cudaEventRecord(ctx.ev[PH_SCATTER + 1], st));
 
@@ -237,23 +244,29 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
     }
     B200_CUDA(cudaEventRecord(ctx.ev[PH_CARRY + 1], st));
 
-    // --- bucket reduction (B and K are powers of two, K <= B)
+    // --- bucket reduction (Br and K are powers of two, K <= Br).  A single bucket set
+    // (precomputed multiples) is cut into V slices that go through the reduction like V windows.
+    const uint32_t V = pre ? (B >= 4096 ? 16u : 1u) : 1u;
+    const uint32_t Br = B / V;
+    const int Wr = pre ? (int)V : Wu;
     uint32_t K = 16;
     while ((M / K) > 65536 && K < 128) K <<= 1;
     if (ctx.opt_reduce_chunk > 0) K = 1u << std::min(ctx.opt_reduce_chunk, 12);
-    K = std::min(K, B);
-    const uint32_t nchunks = B / K;
-    uint32_t log2K = 0;
+    K = std::min(K, Br);
+    const uint32_t nchunks = Br / K;
+    uint32_t log2K = 0, log2Br = 0;
     while ((1u << log2K) < K) log2K++;
-    uint32_t *chunk_T;
-    if (!reserve_as(ctx, SL_CHUNKS, (size_t)Wu * nchunks * R::XW * 4, &chunks)) return false;
-    if (!reserve_as(ctx, SL_CHUNK_TOTALS, (size_t)Wu * nchunks * R::XW * 4, &chunk_T)) return false;
-    if (!reserve_as(ctx, SL_WINDOWS, (size_t)Wu * R::XW * 4, &windows)) return false;
+    while ((1u << log2Br) < Br) log2Br++;
+    uint32_t *chunk_T, *window_T = nullptr;
+    if (!reserve_as(ctx, SL_CHUNKS, (size_t)Wr * nchunks * R::XW * 4, &chunks)) return false;
+    if (!reserve_as(ctx, SL_CHUNK_TOTALS, (size_t)Wr * nchunks * R::XW * 4, &chunk_T)) return false;
+    if (!reserve_as(ctx, SL_WINDOWS, (size_t)2 * Wr * R::XW * 4, &windows)) return false;
+    if (pre) window_T = windows + (size_t)Wr * R::XW;
     if (ctx.tail_pending) {  // the previous range's tail reads chunks / chunk_T / windows
         B200_CUDA(cudaStreamWaitEvent(st, ctx.ev_tail_done, 0));
         ctx.tail_pending = false;
     }
-    k_bucket_reduce<C><<<dim3(cdiv(nchunks, 64), Wu), 64, 0, st>>>(buckets, hist, B, K, chunks, chunk_T);
+    k_bucket_reduce<C><<<dim3(cdiv(nchunks, 64), Wr), 64, 0, st>>>(buckets, hist, Br, K, chunks, chunk_T);
     B200_LAUNCH_CHECK(ctx);
     B200_CUDA(cudaEventRecord(ctx.ev[PH_BUCKET_REDUCE + 1], st));
     constexpr int WR_THREADS = 256;
@@ -270,16 +283,44 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
         B200_CUDA(cudaEventRecord(ctx.ev_tail_go, st));
         B200_CUDA(cudaStreamWaitEvent(ts, ctx.ev_tail_go, 0));
     }
-    k_window_reduce<C, WR_THREADS><<<Wu, WR_THREADS, wr_smem, ts>>>(chunks, chunk_T, nchunks, log2K,
-                                                                   windows);
+    k_window_reduce<C, WR_THREADS><<<Wr, WR_THREADS, wr_smem, ts>>>(chunks, chunk_T, nchunks, log2K,
+                                                                   windows, window_T);
     B200_LAUNCH_CHECK(ctx);
-    k_final<C><<<1, 32, 0, ts>>>(windows, Wu, c, (uint32_t *)d_out);
+    if (pre)
+        k_final_slices<C><<<1, 32, 0, ts>>>(windows, window_T, (int)V, (int)log2Br, (uint32_t *)d_out);
+    else
+        k_final<C><<<1, 32, 0, ts>>>(windows, Wu, c, (uint32_t *)d_out);
     B200_LAUNCH_CHECK(ctx);
     if (ctx.defer_tail) {
         B200_CUDA(cudaEventRecord(ctx.ev_tail_done, ts));
         ctx.tail_pending = true;
     }
     B200_CUDA(cudaEventRecord(ctx.ev[PH_FINAL + 1], st));
+    return true;
+}
+
+// table[w * n + i] = 2^(w c) P_i in device affine form (the multiples the reference's
+// multi_exp_stream_with_precompute reads from its stream, multiexp_stream.hpp:27-41), built on the
+// device: c doublings per step in XYZZ, one batch normalisation per multiple.
+template <class C>
+bool precompute_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, size_t n, int c, int W,
+                     void *d_table) {
+    using R = Raw<C>;
+    if (n == 0 || W <= 0) return true;
+    uint32_t *state, *raw;
+    uint8_t *inf_scratch;
+    if (!reserve_as(ctx, SL_PRE_STATE, n * R::XW * 4, &state)) return false;
+    if (!reserve_as(ctx, SL_PRE_RAW, n * R::PW * 4, &raw)) return false;
+    if (!reserve_as(ctx, SL_TABLE_INF, n, &inf_scratch)) return false;
+    uint32_t *table = (uint32_t *)d_table;
+    B200_CUDA(cudaMemcpyAsync(table, d_aff, n * R::AW * 4, cudaMemcpyDeviceToDevice, ctx.stream));
+    for (int w = 1; w < W; w++) {
+        k_pre_step<C><<<cdiv(n, 128), 128, 0, ctx.stream>>>((const uint32_t *)d_aff, d_inf, state, raw,
+                                                            (uint32_t)n, c, w == 1);
+        B200_LAUNCH_CHECK(ctx);
+        if (!normalise_dev<C>(ctx, raw, n, nullptr, table + (size_t)w * n * R::AW, inf_scratch))
+            return false;
+    }
     return true;
 }
 
@@ -322,6 +363,16 @@ bool wire_decode_impl(Ctx &ctx, const void *d_wire_points, const void *d_wire_sc
 }
 
 template <class C>
+bool stream_decode_impl(Ctx &ctx, const void *d_bytes, size_t n, uint32_t flags, void *d_aff,
+                        uint8_t *d_inf) {
+    if (n == 0) return true;
+    k_stream_decode_points<C><<<cdiv(n, 128), 128, 0, ctx.stream>>>(
+        (const uint8_t *)d_bytes, (uint32_t *)d_aff, d_inf, (uint32_t)n, flags);
+    B200_LAUNCH_CHECK(ctx);
+    return true;
+}
+
+template <class C>
 bool wire_encode_impl(Ctx &ctx, const void *d_raw, void *d_wire_out) {
     k_wire_encode_point<C><<<1, 32, 0, ctx.stream>>>((const uint32_t *)d_raw, (uint8_t *)d_wire_out);
     B200_LAUNCH_CHECK(ctx);
@@ -356,6 +407,8 @@ const GroupOps *make_ops() {
                                  C::Fr::Params::BITS,
                                  &ingest_impl<C>,
                                  &msm_impl<C>,
+                                 &precompute_impl<C>,
+                                 &stream_decode_impl<C>,
                                  &sum_impl<C>,
                                  &to_special_impl<C>,
                                  &batch_exp_impl<C>,

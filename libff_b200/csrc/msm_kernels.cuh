@@ -66,10 +66,16 @@ __device__ __forceinline__ uint32_t warp_cursor_take(uint32_t *cursor, bool vali
 
 // ------------------------------------------------------------------------------------------
 // scalars -> signed digits + histogram.  digits[w * n + i] in [-2^(c-1), 2^(c-1)]
+// bstride = buckets per window (2^(c-1)), or 0 when all windows share ONE bucket set (precomputed
+// multiples 2^(w c) P_i, multiexp_stream.tcc:124-162).  fold_bit >= 0: W c equals the scalar
+// width, so a scalar with bit W c - 1 set would carry out of the top digit (the reference's
+// field_get_signed_digits drops that carry, field_utils.tcc:205-239); such a scalar is replaced
+// by r - s, whose top digit is small, and all its digits change sign: s P = -(r - s) P.
 template <class C>
 __global__ void k_digits(const uint32_t *__restrict__ scalars, const uint8_t *__restrict__ inf_flag,
                          int32_t *__restrict__ digits, uint32_t *__restrict__ hist,
-                         uint32_t *__restrict__ used_windows, uint32_t n, int c, int W) {
+                         uint32_t *__restrict__ used_windows, uint32_t n, int c, int W,
+                         uint32_t bstride, int fold_bit) {
     using Fr = typename C::Fr;
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t top = 0;  // 1 + index of the highest window with a non-zero digit
@@ -77,16 +83,26 @@ __global__ void k_digits(const uint32_t *__restrict__ scalars, const uint8_t *__
         const bool live = i < n;  // every lane runs the loop: the histogram update is warp-wide
         Fr s = live ? Fr::from_mont(Fr::load(scalars + (size_t)i * Fr::N)) : Fr::zero();
         bool skip = !live || (inf_flag != nullptr && inf_flag[i]);
+        bool flip = false;
+        if (fold_bit >= 0) {
+            uint32_t word = 0;
+#pragma unroll
+            for (int k = 0; k < Fr::N; k++)
+                if (k == (fold_bit >> 5)) word = s.v[k];
+            flip = (word >> (fold_bit & 31)) & 1u;
+            if (flip) s = Fr::neg(s);
+        }
         const uint32_t mask = (1u << c) - 1, half = 1u << (c - 1);
         uint32_t carry = 0;
         for (int w = 0; w < W; w++) {
             uint32_t d = (s.v[0] & mask) + carry;
             carry = d > half;
             int32_t sd = (int32_t)d - (int32_t)(carry << c);
+            if (flip) sd = -sd;
             if (skip) sd = 0;
             if (live) digits[(size_t)w * n + i] = sd;
             if (sd != 0) top = w + 1;
-            warp_hist_add(hist, sd != 0, (uint32_t)w * half + (uint32_t)(sd < 0 ? -sd : sd) - 1);
+            warp_hist_add(hist, sd != 0, (uint32_t)w * bstride + (uint32_t)(sd < 0 ? -sd : sd) - 1);
 #pragma unroll
             for (int k = 0; k < Fr::N - 1; k++) s.v[k] = __funnelshift_r(s.v[k], s.v[k + 1], c);
             s.v[Fr::N - 1] >>= c;
@@ -187,17 +203,20 @@ static __global__ void __launch_bounds__(SCAN_THREADS)
 }
 
 // ------------------------------------------------------------------------------------------
+// item = index of the point to add: i for the plain MSM (pstride 1, wstride 0); the position of
+// 2^(w c) P_i in a precomputed table otherwise (i * pstride + w * wstride).
 template <class C>
 __global__ void k_scatter(const int32_t *__restrict__ digits, uint32_t *__restrict__ cursor,
                           Entry *__restrict__ sorted, uint32_t *__restrict__ seg_bucket,
-                          uint32_t n, int c, uint32_t SEG) {
+                          uint32_t n, uint32_t SEG, uint32_t bstride, uint32_t pstride,
+                          uint32_t wstride) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t w = blockIdx.y;
     const int32_t d = i < n ? digits[(size_t)w * n + i] : 0;
-    const uint32_t b = (w << (c - 1)) + (uint32_t)(d < 0 ? -d : d) - 1;
+    const uint32_t b = w * bstride + (uint32_t)(d < 0 ? -d : d) - 1;
     const uint32_t pos = warp_cursor_take(cursor, d != 0, b);  // all lanes take part
     if (d == 0) return;
-    sorted[pos] = i | (d < 0 ? 0x80000000u : 0u);
+    sorted[pos] = (i * pstride + w * wstride) | (d < 0 ? 0x80000000u : 0u);
     // every position is written exactly once, so exactly one thread sees each segment start
     if (pos % SEG == 0) seg_bucket[pos / SEG] = b;
 }
@@ -361,7 +380,8 @@ __global__ void __launch_bounds__(64)
 template <class C, int THREADS>
 __global__ void __launch_bounds__(THREADS)
     k_window_reduce(const uint32_t *__restrict__ chunk_L, const uint32_t *__restrict__ chunk_T,
-                    uint32_t chunks, uint32_t log2K, uint32_t *__restrict__ window_sums) {
+                    uint32_t chunks, uint32_t log2K, uint32_t *__restrict__ window_sums,
+                    uint32_t *__restrict__ window_totals) {
     using R = Raw<C>;
     using F = typename C::Fq;
     using X = XYZZ<F>;
@@ -369,7 +389,7 @@ __global__ void __launch_bounds__(THREADS)
     const uint32_t w = blockIdx.x, t = threadIdx.x;
     const uint32_t Q = chunks > (uint32_t)THREADS ? chunks / THREADS : 1u;
     const uint32_t log2Q = 31 - __clz(Q);
-    X total = X::inf();
+    X total = X::inf(), plain = X::inf();
     if (t * Q < chunks) {
         X sumL = X::inf(), run = X::inf(), acc = X::inf();
         for (uint32_t j = (t + 1) * Q; j-- > t * Q;) {
@@ -380,6 +400,7 @@ __global__ void __launch_bounds__(THREADS)
             q = X::load(chunk_L + g);
             X::add(sumL, q);
         }
+        plain = run;
         X y = small_mul<F>(run, t);
         for (uint32_t k = 0; k < log2Q; k++) y = X::dbl(y);
         X::add(y, acc);
@@ -398,6 +419,20 @@ __global__ void __launch_bounds__(THREADS)
         __syncthreads();
     }
     if (t == 0) total.store(window_sums + (size_t)w * R::XW);
+    if (window_totals == nullptr) return;  // uniform across the block
+    // the unweighted sum of the window's buckets (used when one bucket set is cut into slices)
+    __syncthreads();
+    plain.store(smem + (size_t)t * R::XW);
+    __syncthreads();
+    for (uint32_t d = THREADS / 2; d > 0; d >>= 1) {
+        if (t < d) {
+            X q = X::load(smem + (size_t)(t + d) * R::XW);
+            X::add(plain, q);
+            plain.store(smem + (size_t)t * R::XW);
+        }
+        __syncthreads();
+    }
+    if (t == 0) plain.store(window_totals + (size_t)w * R::XW);
 }
 
 // One doubling shared by the lanes of a warp.  The c doublings between windows are a serial
@@ -457,6 +492,65 @@ __global__ void __launch_bounds__(32) k_final(const uint32_t *__restrict__ windo
         R::from_xyzz(r, Xo, Yo, Zo);
         R::store(out_raw, Xo, Yo, Zo);
     }
+}
+
+// Single bucket set (precomputed multiples) cut into V slices of 2^log2S consecutive buckets that
+// went through the reduction like V windows: slice g contributed S_g = sum (b_local + 1) bucket and
+// T_g = sum bucket, and the set's value is  sum_g S_g + 2^log2S * sum_g g T_g  (running sums from
+// the top slice, then log2S doublings).
+template <class C>
+__global__ void __launch_bounds__(32)
+    k_final_slices(const uint32_t *__restrict__ slice_sums, const uint32_t *__restrict__ slice_totals,
+                   int V, int log2S, uint32_t *__restrict__ out_raw) {
+    using R = Raw<C>;
+    using F = typename C::Fq;
+    using X = XYZZ<F>;
+    __shared__ __align__(16) uint32_t sh[4 * F::N];
+    if (blockIdx.x != 0) return;
+    const uint32_t lane = threadIdx.x & 31;
+    X run = X::inf(), acc = X::inf(), sumS = X::inf();
+    for (int g = V - 1; g >= 0; g--) {
+        X q = X::load(slice_sums + (size_t)g * R::XW);
+        X::add(sumS, q);
+        if (g > 0) {
+            q = X::load(slice_totals + (size_t)g * R::XW);
+            X::add(run, q);
+            X::add(acc, run);
+        }
+    }
+    if (!acc.is_inf())  // uniform across the warp
+        for (int k = 0; k < log2S; k++) acc = dbl_coop<F>(acc, sh, lane);
+    X::add(acc, sumS);
+    if (lane == 0) {
+        F Xo, Yo, Zo;
+        R::from_xyzz(acc, Xo, Yo, Zo);
+        R::store(out_raw, Xo, Yo, Zo);
+    }
+}
+
+// One step of a table build: state[i] <- 2^c state[i] (state = the base itself when `first`),
+// also written in the reference's layout for the batch normalisation that makes it affine.
+template <class C>
+__global__ void __launch_bounds__(128)
+    k_pre_step(const uint32_t *__restrict__ aff, const uint8_t *__restrict__ inf_flag,
+               uint32_t *__restrict__ state, uint32_t *__restrict__ raw, uint32_t n, int c,
+               bool first) {
+    using R = Raw<C>;
+    using F = typename C::Fq;
+    using X = XYZZ<F>;
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    X p;
+    if (first) {
+        p = inf_flag[i] ? X::inf() : X::from_affine(Affine<F>::load(aff + (size_t)i * R::AW));
+    } else {
+        p = X::load(state + (size_t)i * R::XW);
+    }
+    for (int k = 0; k < c; k++) p = X::dbl(p);
+    p.store(state + (size_t)i * R::XW);
+    F Xo, Yo, Zo;
+    R::from_xyzz(p, Xo, Yo, Zo);
+    R::store(raw + (size_t)i * R::PW, Xo, Yo, Zo);
 }
 
 // Sum of `count` reference-layout group elements (partials of the GPU shards, multiexp.tcc:681-685)

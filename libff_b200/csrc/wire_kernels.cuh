@@ -196,6 +196,43 @@ __global__ void __launch_bounds__(128)
     if (e) atomicOr(err, e);
 }
 
+// ---- libff's binary stream encoding (what multi_exp_stream reads) -------------------------------
+// group_element_codec<encoding_binary, Form, compression_off> (curve_serialization.tcc:79-101):
+// X then Y; an extension-field coordinate is coeffs[0] then coeffs[1] (field_serialization.tcc:
+// 127-147); every prime-field element is its bigint with ALL bytes reversed, i.e. big-endian
+// (:197-222), holding the plain value (form_plain) or the Montgomery representation
+// (form_montgomery).  X = 0 and Y = 1 encodes the zero element.  Like the reference's reader, no
+// range or curve check is made.
+template <class P>
+B200_DEV void stream_read_coord(const uint8_t *src, bool mont, Fp<P> &out) {
+    Fp<P> v;
+    (void)wire_read_fp<P>(src, v);
+    out = mont ? v : Fp<P>::to_mont(v);
+}
+template <class P, int NR>
+B200_DEV void stream_read_coord(const uint8_t *src, bool mont, Fp2<P, NR> &out) {
+    stream_read_coord<P>(src, mont, out.c0);  // lowest order first
+    stream_read_coord<P>(src + 4 * P::N, mont, out.c1);
+}
+
+template <class C>
+__global__ void __launch_bounds__(128)
+    k_stream_decode_points(const uint8_t *__restrict__ bytes, uint32_t *__restrict__ aff,
+                           uint8_t *__restrict__ inf_flag, uint32_t n, uint32_t flags) {
+    using R = Raw<C>;
+    using F = typename C::Fq;
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    constexpr size_t CB = (size_t)R::CW * 4;
+    F x, y;
+    stream_read_coord(bytes + (size_t)i * 2 * CB, (flags & 1u) != 0, x);
+    stream_read_coord(bytes + (size_t)i * 2 * CB + CB, (flags & 1u) != 0, y);
+    const bool inf = x.is_zero() && y == F::one();
+    Affine<F> a{inf ? F::zero() : x, inf ? F::zero() : y};
+    a.store(aff + (size_t)i * R::AW);
+    inf_flag[i] = inf;
+}
+
 // scalars: wire -> Montgomery limbs (what the MSM pipeline takes)
 template <class C>
 __global__ void k_wire_decode_scalars(const uint8_t *__restrict__ wire, uint32_t *__restrict__ scalars,

@@ -80,6 +80,9 @@ def lib():
             "ref_wire_group_read": (sz, [i32, vp, vp, vp, sz]),
             "ref_wire_scalar_write": (sz, [i32, vp, vp, sz]),
             "ref_wire_scalar_read": (sz, [i32, vp, vp, vp, sz]),
+            "ref_stream_write": (sz, [i32, i32, vp, sz, sz, vp]),
+            "ref_multi_exp_stream": (i32, [i32, i32, vp, sz, vp, sz, sz, vp, i32]),
+            "ref_bdlo12_signed_optimal_c": (sz, [sz]),
         }
         for name, (res, args) in sigs.items():
             f = getattr(L, name)
@@ -254,3 +257,38 @@ def wire_scalar_read(gid, data: bytes):
     lib().ref_wire_scalar_read(gid, a.ctypes.data_as(C.c_void_p), _p(out),
                                okv.ctypes.data_as(C.c_void_p), n)
     return out, okv.astype(bool)
+
+
+# ---- streamed / precomputed MSM (multiexp_stream.tcc:164-223) ------------------------------------
+FORM_PLAIN, FORM_MONTGOMERY = 0, 1   # form_t of the binary stream encoding
+
+
+def stream_write(gid, pts, form=FORM_MONTGOMERY, precompute_c=0) -> bytes:
+    """group_write<encoding_binary, form, compression_off> of every element; with precompute_c each
+    base is followed by its multiples 2^c, 2^2c, ... (profile_multiexp.cpp:120-151)."""
+    a = _c(pts)
+    n = a.shape[0]
+    size = lib().ref_stream_write(gid, form, _p(a), n, precompute_c, None)
+    out = np.zeros(size, dtype=np.uint8)
+    lib().ref_stream_write(gid, form, _p(a), n, precompute_c, out.ctypes.data_as(C.c_void_p))
+    return out.tobytes()
+
+
+def multi_exp_stream(gid, data: bytes, scalars, form=FORM_MONTGOMERY, precompute_c=0,
+                     normalize=True) -> np.ndarray:
+    """multi_exp_stream (precompute_c == 0) / multi_exp_stream_with_precompute on the bytes.
+    Returns None where the reference's own behaviour is undefined: it sums the buckets of every
+    digit position without checking that one is non-empty (multiexp.tcc:88-106), so an all-zero
+    top position -- e.g. bw6_761's 377-bit scalars with c = 7 -- reads out of bounds."""
+    s = _c(scalars)
+    buf = np.frombuffer(data, dtype=np.uint8)
+    out = np.zeros(group_words(gid), dtype=np.uint64)
+    rc = lib().ref_multi_exp_stream(gid, form, buf.ctypes.data_as(C.c_void_p), len(data), _p(s),
+                                    s.shape[0], precompute_c, _p(out), int(normalize))
+    if rc < 0:
+        raise ValueError("ref_multi_exp_stream: unknown group")
+    return out if rc == 1 else None
+
+
+def bdlo12_signed_optimal_c(n) -> int:
+    return int(lib().ref_bdlo12_signed_optimal_c(n))

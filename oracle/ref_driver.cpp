@@ -21,6 +21,7 @@
 //   SHA512_rng                    libff/common/rng.tcc:26-71
 //   ffi::group_element_read/write, field_element_read/write   ffi/ffi_serialization.tcc:98-187
 #include <cstdint>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -30,6 +31,8 @@
 #include <libff/algebra/curves/bw6_761/bw6_761_pp.hpp>
 #include <libff/algebra/fields/field_utils.hpp>
 #include <libff/algebra/scalar_multiplication/multiexp.hpp>
+#include <libff/algebra/scalar_multiplication/multiexp_stream.hpp>
+#include <sstream>
 #include <libff/common/profiling.hpp>
 #include <libff/common/rng.hpp>
 
@@ -676,4 +679,148 @@ size_t ref_wire_scalar_read(int gid, const void *in, void *out, uint8_t *okv, si
     }
     return 0;
 }
+}
+
+// ---- streamed / precomputed MSM (multiexp_stream.tcc:164-223) and the binary stream encoding it
+// reads (curve_serialization.tcc:79-101), uncompressed, form 0 = plain, 1 = montgomery ----
+template<typename G, form_t Form> static size_t stream_write_t(const void *in, size_t n, size_t c, void *out)
+{
+    using Fr = typename G::scalar_field;
+    std::ostringstream os(std::ios_base::out | std::ios_base::binary);
+    const size_t per = c ? (Fr::num_bits + c - 1) / c : 1;
+    for (size_t i = 0; i < n; ++i) {
+        G el;
+        std::memcpy((void *)&el, (const char *)in + i * sizeof(G), sizeof(G));
+        // profile_multiexp.cpp:137-147: the element, then each further multiple by 2^c
+        group_write<encoding_binary, Form, compression_off>(el, os);
+        for (size_t k = 1; k < per; ++k) {
+            for (size_t j = 0; j < c; ++j) {
+                el = el.dbl();
+            }
+            group_write<encoding_binary, Form, compression_off>(el, os);
+        }
+    }
+    const std::string b = os.str();
+    if (out) {
+        std::memcpy(out, b.data(), b.size());
+    }
+    return b.size();
+}
+// multiexp_accumulate_buckets requires a non-empty bucket ("Caller must ensure that at least one
+// bucket is not empty", multiexp.tcc:88-89, an assert that NDEBUG removes); the stream functions
+// call it for EVERY digit position (multiexp_stream.tcc:96-118), also the top ones that hold
+// nothing but a possible carry, and for the single bucket set of the precompute variant.  Where
+// that precondition fails the reference reads bucket_hit[-1...]: undefined, no value to compare to.
+template<typename Fr> static bool stream_msm_defined(const std::vector<Fr> &ex, size_t c, size_t num_digits, bool per_round)
+{
+    std::vector<ssize_t> digits(num_digits);
+    std::vector<bool> hit(num_digits, false);
+    bool any = false;
+    for (const Fr &e : ex) {
+        field_get_signed_digits(digits, e, c, num_digits);
+        for (size_t k = 0; k < num_digits; ++k) {
+            if (digits[k] != 0) {
+                hit[k] = true;
+                any = true;
+            }
+        }
+    }
+    if (!per_round) {
+        return any;
+    }
+    for (size_t k = 0; k < num_digits; ++k) {
+        if (!hit[k]) {
+            return false;
+        }
+    }
+    return true;
+}
+
+template<typename G, form_t Form>
+static int stream_msm_t(const void *bytes, size_t nbytes, const void *scalars, size_t n, size_t c,
+                        void *out, int normalize)
+{
+    using Fr = typename G::scalar_field;
+    std::istringstream is(std::string((const char *)bytes, nbytes), std::ios_base::in | std::ios_base::binary);
+    const std::vector<Fr> ex = load_vec<Fr>(scalars, n);
+    // multi_exp_stream / multi_exp_stream_with_precompute (multiexp_stream.tcc:164-223) run their
+    // reader in a second thread over an SPSC FIFO whose counters are relaxed atomics: the element
+    // data is not published to the consumer and the call crashes now and then (seen here on
+    // bw6_761).  A checker must be deterministic, so the SAME reference reader and the SAME
+    // reference consumer are called one after the other on a FIFO that holds every element;
+    // set REF_STREAM_THREADED=1 to go through the two-thread entry points instead.
+    G r;
+    const bool threaded = std::getenv("REF_STREAM_THREADED") != nullptr;
+    if (c ? !stream_msm_defined(ex, c, (Fr::num_bits + c - 1) / c, false)
+          : !stream_msm_defined(
+                ex, bdlo12_signed_optimal_c(n), (Fr::num_bits + 2 + bdlo12_signed_optimal_c(n) - 1) / bdlo12_signed_optimal_c(n), true)) {
+        return 0;
+    }
+    if (threaded) {
+        r = c ? multi_exp_stream_with_precompute<Form, compression_off, G, Fr>(is, ex, c)
+              : multi_exp_stream<Form, compression_off, G, Fr>(is, ex);
+    } else if (c) {
+        const size_t num_digits = (Fr::num_bits + c - 1) / c;  // multiexp_stream.tcc:205
+        concurrent_buffer_fifo_spsc<G> fifo(std::max<size_t>(n, 1), num_digits);
+        element_buffers_from_stream_producer<Form, compression_off, G>(is, fifo, n, num_digits);
+        r = multi_exp_precompute_from_fifo<G, Fr>(fifo, ex, c, num_digits);
+    } else {
+        const size_t cc = bdlo12_signed_optimal_c(n);  // multiexp_stream.tcc:170
+        concurrent_fifo_spsc<G> fifo(std::max<size_t>(n, 1));
+        elements_from_stream_producer<Form, compression_off, G>(is, fifo, n);
+        r = multi_exp_base_elements_from_fifo_all_rounds<G, Fr>(fifo, ex, cc);
+    }
+    if (normalize) {
+        r.to_affine_coordinates();
+    }
+    std::memcpy(out, (const void *)&r, sizeof(G));
+    return 1;
+}
+template<typename G> static size_t stream_write_g(int form, const void *in, size_t n, size_t c, void *out)
+{
+    return form ? stream_write_t<G, form_montgomery>(in, n, c, out) : stream_write_t<G, form_plain>(in, n, c, out);
+}
+template<typename G>
+static int stream_msm_g(int form, const void *bytes, size_t nbytes, const void *scalars, size_t n, size_t c,
+                        void *out, int normalize)
+{
+    return form ? stream_msm_t<G, form_montgomery>(bytes, nbytes, scalars, n, c, out, normalize)
+                : stream_msm_t<G, form_plain>(bytes, nbytes, scalars, n, c, out, normalize);
+}
+
+extern "C" {
+// bytes written (out may be NULL to size the buffer); c != 0: every base followed by its multiples
+size_t ref_stream_write(int gid, int form, const void *in, size_t n, size_t c, void *out)
+{
+    switch (gid) {
+    case 0: return stream_write_g<alt_bn128_G1>(form, in, n, c, out);
+    case 1: return stream_write_g<alt_bn128_G2>(form, in, n, c, out);
+    case 2: return stream_write_g<bls12_377_G1>(form, in, n, c, out);
+    case 3: return stream_write_g<bw6_761_G1>(form, in, n, c, out);
+    case 4: return stream_write_g<bls12_377_G2>(form, in, n, c, out);
+    case 5: return stream_write_g<bw6_761_G2>(form, in, n, c, out);
+    case 6: return stream_write_g<bls12_381_G1>(form, in, n, c, out);
+    case 7: return stream_write_g<bls12_381_G2>(form, in, n, c, out);
+    }
+    return 0;
+}
+// multi_exp_stream (c == 0) / multi_exp_stream_with_precompute (c != 0) on an in-memory stream;
+// 1 = computed, 0 = the reference's behaviour is undefined for this input (see stream_msm_defined),
+// -1 = unknown group
+int ref_multi_exp_stream(int gid, int form, const void *bytes, size_t nbytes, const void *scalars, size_t n,
+                         size_t c, void *out, int normalize)
+{
+    switch (gid) {
+    case 0: return stream_msm_g<alt_bn128_G1>(form, bytes, nbytes, scalars, n, c, out, normalize);
+    case 1: return stream_msm_g<alt_bn128_G2>(form, bytes, nbytes, scalars, n, c, out, normalize);
+    case 2: return stream_msm_g<bls12_377_G1>(form, bytes, nbytes, scalars, n, c, out, normalize);
+    case 3: return stream_msm_g<bw6_761_G1>(form, bytes, nbytes, scalars, n, c, out, normalize);
+    case 4: return stream_msm_g<bls12_377_G2>(form, bytes, nbytes, scalars, n, c, out, normalize);
+    case 5: return stream_msm_g<bw6_761_G2>(form, bytes, nbytes, scalars, n, c, out, normalize);
+    case 6: return stream_msm_g<bls12_381_G1>(form, bytes, nbytes, scalars, n, c, out, normalize);
+    case 7: return stream_msm_g<bls12_381_G2>(form, bytes, nbytes, scalars, n, c, out, normalize);
+    }
+    return -1;
+}
+size_t ref_bdlo12_signed_optimal_c(size_t n) { return bdlo12_signed_optimal_c(n); }
 }
