@@ -13,6 +13,9 @@
  *   libff::batch_exp<G, Fr>(scalar_size, window, table, v[, num_entries])
  *                                                   multiexp.hpp:120-134, multiexp.tcc:875-915
  *   libff::batch_to_special<G>(vec)                 multiexp.hpp:144, multiexp.tcc:949-974
+ *   libff::multi_exp_stream<Form, Comp, G, Fr>(istream, exponents)
+ *   libff::multi_exp_stream_with_precompute<Form, Comp, G, Fr>(istream, exponents, c)
+ *                                                   multiexp_stream.hpp:19-41, .tcc:164-223
  *
  * for G in { alt_bn128_G1, alt_bn128_G2, bls12_377_G1, bw6_761_G1 } (the path's four groups) and
  * { bls12_377_G2, bw6_761_G2, bls12_381_G1, bls12_381_G2 } (bls12_381 is in the
@@ -41,7 +44,10 @@
 #include <libff/algebra/curves/bls12_381/bls12_381_pp.hpp>
 #include <libff/algebra/curves/bw6_761/bw6_761_pp.hpp>
 #include <libff/algebra/scalar_multiplication/multiexp.hpp>
+#include <libff/algebra/scalar_multiplication/multiexp_stream.hpp>
+#include <istream>
 #include <mutex>
+#include <thread>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -209,6 +215,95 @@ template<typename GroupT> void batch_to_special(std::vector<GroupT> &vec)
     }
 }
 
+/// multi_exp_stream / multi_exp_stream_with_precompute (multiexp_stream.tcc:164-223): the base
+/// elements are read from the stream in chunks by a helper thread (the reference's producer
+/// thread, :176-180) while the device reduces the previous chunk.  Uncompressed streams are
+/// uploaded as bytes and decoded on the device; compressed ones are decoded by libff's own
+/// group_read (a square root per element) and pushed as in-memory elements.
+/// precompute_c == 0: plain stream.
+template<form_t Form, compression_t Comp, typename GroupT, typename FieldT>
+GroupT multi_exp_stream(
+    std::istream &in_s, const std::vector<FieldT> &exponents, const size_t precompute_c)
+{
+    (void)sizeof(layout_check<GroupT, FieldT>);
+    const size_t n = exponents.size();
+    if (n == 0) {
+        return GroupT::zero();
+    }
+    ensure_init();
+    const uint32_t gid = group_id<GroupT>::value;
+    const size_t per = precompute_c ? b200msm_precompute_digits(gid, (uint32_t)precompute_c) : 1;
+    if (per == 0) {
+        throw std::runtime_error("b200 multi_exp_stream: unsupported precompute_c");
+    }
+    const bool raw_bytes = Comp == compression_off;
+    const uint32_t encoding =
+        !raw_bytes ? B200MSM_STREAM_MEMORY_SPECIAL
+                   : (Form == form_montgomery ? B200MSM_STREAM_BINARY_MONTGOMERY
+                                              : B200MSM_STREAM_BINARY_PLAIN);
+    const size_t elem_bytes = raw_bytes ? b200msm_wire_point_bytes(gid) : sizeof(GroupT);
+    uint64_t stream = 0;
+    if (!b200msm_stream_begin(
+            gid,
+            (const void *)exponents.data(),
+            n * sizeof(FieldT),
+            n,
+            encoding,
+            (uint32_t)precompute_c,
+            &stream)) {
+        fail("b200msm_stream_begin");
+    }
+    // bases per chunk: large enough to amortise the fixed cost of one device MSM
+    const size_t chunk = std::max<size_t>(1, std::min<size_t>(n, ((size_t)1 << 20) / per));
+    std::vector<char> buf[2];
+    buf[0].resize(chunk * per * elem_bytes);
+    buf[1].resize(chunk * per * elem_bytes);
+    bool read_ok = true;
+    auto read_chunk = [&](std::vector<char> &dst, size_t count) {
+        if (raw_bytes) {
+            in_s.read(dst.data(), (std::streamsize)(count * per * elem_bytes));
+            if (!in_s) {
+                read_ok = false;
+            }
+        } else {
+            GroupT *g = (GroupT *)dst.data();
+            for (size_t i = 0; i < count * per; ++i) {
+                new (g + i) GroupT(); // buffers are raw storage
+                group_read<encoding_binary, Form, Comp>(g[i], in_s);
+            }
+        }
+    };
+    size_t done = 0, cur = 0;
+    size_t count = std::min(chunk, n);
+    read_chunk(buf[cur], count);
+    bool ok = true;
+    while (ok && read_ok && done < n) {
+        const size_t next_count = std::min(chunk, n - done - count);
+        std::thread reader;
+        if (next_count) {
+            reader = std::thread([&, next_count] { read_chunk(buf[cur ^ 1], next_count); });
+        }
+        ok = b200msm_stream_push(stream, buf[cur].data(), count * per * elem_bytes, count);
+        if (reader.joinable()) {
+            reader.join();
+        }
+        done += count;
+        count = next_count;
+        cur ^= 1;
+    }
+    GroupT result;
+    if (!ok || !read_ok) {
+        const std::string why = ok ? "stream ended early" : b200msm_last_error();
+        GroupT scratch;
+        (void)b200msm_stream_finish(stream, (void *)&scratch, sizeof(GroupT)); // releases it
+        throw std::runtime_error("b200 multi_exp_stream: " + why);
+    }
+    if (!b200msm_stream_finish(stream, (void *)&result, sizeof(GroupT))) {
+        fail("b200msm_stream_finish");
+    }
+    return result;
+}
+
 } // namespace b200
 } // namespace libff
 
@@ -259,7 +354,31 @@ template<typename GroupT> void batch_to_special(std::vector<GroupT> &vec)
     }                                                                                         \
     }
 
+#define LIBFF_B200_SPECIALISE_STREAM(G, F, FORM, COMP)                                        \
+    namespace libff                                                                           \
+    {                                                                                         \
+    template<>                                                                                \
+    inline G multi_exp_stream<FORM, COMP, G, F>(                                              \
+        std::istream & base_elements_in, const std::vector<F> &exponents)                     \
+    {                                                                                         \
+        return b200::multi_exp_stream<FORM, COMP, G, F>(base_elements_in, exponents, 0);      \
+    }                                                                                         \
+    template<>                                                                                \
+    inline G multi_exp_stream_with_precompute<FORM, COMP, G, F>(                              \
+        std::istream & precomputed_elements_in,                                               \
+        const std::vector<F> &exponents,                                                      \
+        const size_t precompute_c)                                                            \
+    {                                                                                         \
+        return b200::multi_exp_stream<FORM, COMP, G, F>(                                      \
+            precomputed_elements_in, exponents, precompute_c);                                \
+    }                                                                                         \
+    }
+
 #define LIBFF_B200_SPECIALISE_GROUP(G, F)                                                     \
+    LIBFF_B200_SPECIALISE_STREAM(G, F, form_plain, compression_off)                           \
+    LIBFF_B200_SPECIALISE_STREAM(G, F, form_plain, compression_on)                            \
+    LIBFF_B200_SPECIALISE_STREAM(G, F, form_montgomery, compression_off)                      \
+    LIBFF_B200_SPECIALISE_STREAM(G, F, form_montgomery, compression_on)                       \
     LIBFF_B200_SPECIALISE_MULTI_EXP(G, F, multi_exp_method_BDLO12, multi_exp_base_form_normal) \
     LIBFF_B200_SPECIALISE_MULTI_EXP(G, F, multi_exp_method_BDLO12, multi_exp_base_form_special) \
     LIBFF_B200_SPECIALISE_MULTI_EXP(                                                          \
@@ -303,6 +422,7 @@ LIBFF_B200_SPECIALISE_GROUP(bls12_381_G1, bls12_381_Fr)
 LIBFF_B200_SPECIALISE_GROUP(bls12_381_G2, bls12_381_Fr)
 
 #undef LIBFF_B200_SPECIALISE_GROUP
+#undef LIBFF_B200_SPECIALISE_STREAM
 #undef LIBFF_B200_SPECIALISE_MULTI_EXP
 
 #endif // LIBFF_B200_HPP_

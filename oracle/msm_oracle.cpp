@@ -576,6 +576,157 @@ static G bdlo12_signed_inner(const G *bases, const Fr *exps, size_t n) {
     return result;
 }
 
+// ------------------------------------------------------------------------------------------------
+// Streamed MSM (multiexp_stream.tcc) and the binary stream encoding it reads.
+
+template <class F>
+static size_t field_num_bits() {  // Fp_model::num_bits = bit length of the modulus
+    Big<F::N> m;
+    memcpy(m.d, F::P.mod, sizeof m.d);
+    return m.num_bits();
+}
+
+// field_get_signed_digits (field_utils.tcc:205-239): one pass, num_digits digits; a carry out of
+// the last digit is dropped, exactly as the reference does
+template <int N>
+static void get_signed_digits(std::vector<long> &digits, const Big<N> &v, size_t c, size_t num_digits) {
+    const size_t carry_mask = (size_t)1 << (c - 1), overflow_mask = (size_t)1 << c;
+    size_t carry = 0, overflow = 0;
+    for (size_t k = 0; k < num_digits; k++) {
+        carry = overflow | carry;
+        const size_t digit = get_digit(v, c, k) + carry;
+        overflow = (digit & overflow_mask) >> c;
+        carry = (digit & carry_mask) >> (c - 1);
+        digits[k] = (long)((1 - overflow) * (digit - carry * overflow_mask));
+    }
+}
+
+// multi_exp_add_element_to_bucket_with_signed_digit<special> (multiexp.tcc:45-81)
+template <class G>
+static void add_to_bucket(std::vector<G> &buckets, std::vector<bool> &hit, const G &el, long digit) {
+    if (digit == 0) return;
+    const size_t b = (size_t)(digit < 0 ? -digit : digit) - 1;
+    const G e = digit < 0 ? -el : el;
+    if (hit[b]) {
+        buckets[b] = buckets[b].mixed_add(e);
+    } else {
+        buckets[b] = e;
+        hit[b] = true;
+    }
+}
+
+// multiexp_accumulate_buckets<normal> (multiexp.tcc:90-125).  *defined = false when no bucket is
+// set: the reference requires one (":88-89 Caller must ensure ...") and reads out of bounds otherwise.
+template <class G>
+static G accumulate_buckets(const std::vector<G> &buckets, const std::vector<bool> &hit, bool *defined) {
+    size_t i = buckets.size();
+    while (i > 0 && !hit[i - 1]) --i;
+    if (i == 0) {
+        *defined = false;
+        return G::zero();
+    }
+    --i;
+    G sum = buckets[i], acc = buckets[i];
+    while (i > 0) {
+        --i;
+        if (hit[i]) acc = acc + buckets[i];
+        sum = sum + acc;
+    }
+    return sum;
+}
+
+// multi_exp_base_elements_from_fifo_all_rounds (multiexp_stream.tcc:51-122) with
+// c = bdlo12_signed_optimal_c(n) (:170, multiexp.tcc:636-640)
+template <class G, class Fr>
+static G stream_all_rounds(const G *bases, const Fr *exps, size_t n, bool *defined) {
+    const size_t c = pippenger_optimal_c(n) + 1;
+    const size_t num_digits = (field_num_bits<Fr>() + 2 + c - 1) / c;
+    const size_t num_buckets = (size_t)1 << (c - 1);
+    std::vector<std::vector<G>> buckets(num_digits, std::vector<G>(num_buckets, G::zero()));
+    std::vector<std::vector<bool>> hit(num_digits, std::vector<bool>(num_buckets, false));
+    std::vector<long> digits(num_digits);
+    for (size_t i = 0; i < n; i++) {
+        Big<Fr::N> bi;
+        exps[i].as_bigint(bi.d);
+        get_signed_digits(digits, bi, c, num_digits);
+        for (size_t k = 0; k < num_digits; k++) add_to_bucket(buckets[k], hit[k], bases[i], digits[k]);
+    }
+    G result = accumulate_buckets(buckets[num_digits - 1], hit[num_digits - 1], defined);
+    for (size_t k = num_digits - 1; k-- > 0;) {
+        for (size_t i = 0; i < c; i++) result = result.dbl();
+        result = result + accumulate_buckets(buckets[k], hit[k], defined);
+    }
+    return result;
+}
+
+// multi_exp_precompute_from_fifo (multiexp_stream.tcc:124-162): table holds, per base, its
+// num_digits multiples by 2^(k c); ONE bucket set
+template <class G, class Fr>
+static G stream_precompute(const G *table, const Fr *exps, size_t n, size_t c, bool *defined) {
+    const size_t num_digits = (field_num_bits<Fr>() + c - 1) / c;  // :205
+    const size_t num_buckets = (size_t)1 << (c - 1);
+    std::vector<G> buckets(num_buckets, G::zero());
+    std::vector<bool> hit(num_buckets, false);
+    std::vector<long> digits(num_digits);
+    for (size_t i = 0; i < n; i++) {
+        Big<Fr::N> bi;
+        exps[i].as_bigint(bi.d);
+        get_signed_digits(digits, bi, c, num_digits);
+        for (size_t k = 0; k < num_digits; k++)
+            add_to_bucket(buckets, hit, table[i * num_digits + k], digits[k]);
+    }
+    return accumulate_buckets(buckets, hit, defined);
+}
+
+// field_element_codec<encoding_binary, Form, Fp_model> (field_serialization.tcc:197-222): the
+// bigint (plain value or mont_repr) with all its bytes reversed; extension fields coefficient by
+// coefficient, lowest first (:127-147)
+template <int N, int ID>
+static void stream_put(std::vector<uint8_t> &out, const Fp<N, ID> &x, bool mont) {
+    uint64_t w[N];
+    if (mont) {
+        memcpy(w, x.v, sizeof w);
+    } else {
+        x.as_bigint(w);
+    }
+    const uint8_t *b = (const uint8_t *)w;
+    for (size_t k = sizeof w; k-- > 0;) out.push_back(b[k]);
+}
+template <class F>
+static void stream_put(std::vector<uint8_t> &out, const Fp2<F> &x, bool mont) {
+    stream_put(out, x.c0, mont);
+    stream_put(out, x.c1, mont);
+}
+template <int N, int ID>
+static const uint8_t *stream_get(const uint8_t *in, Fp<N, ID> &x, bool mont) {
+    uint64_t w[N];
+    uint8_t *b = (uint8_t *)w;
+    for (size_t k = 0; k < sizeof w; k++) b[sizeof w - 1 - k] = in[k];
+    x = mont ? Fp<N, ID>::zero() : Fp<N, ID>::from_bigint(w);
+    if (mont) memcpy(x.v, w, sizeof w);
+    return in + sizeof w;
+}
+template <class F>
+static const uint8_t *stream_get(const uint8_t *in, Fp2<F> &x, bool mont) {
+    in = stream_get(in, x.c0, mont);
+    return stream_get(in, x.c1, mont);
+}
+// group_element_codec<encoding_binary, Form, compression_off> (curve_serialization.tcc:79-101)
+template <class G>
+static void stream_put_point(std::vector<uint8_t> &out, G p, bool mont) {
+    p.to_special();  // to_affine_coordinates: zero becomes (0, 1, 0)
+    stream_put(out, p.X, mont);
+    stream_put(out, p.Y, mont);
+}
+template <class G>
+static const uint8_t *stream_get_point(const uint8_t *in, G &p, bool mont) {
+    in = stream_get(in, p.X, mont);
+    in = stream_get(in, p.Y, mont);
+    typedef decltype(p.X) F;
+    p.Z = (p.X.is_zero() && p.Y == F::one()) ? F::zero() : F::one();
+    return in;
+}
+
 // libff::multi_exp (multiexp.tcc:643-688): `chunks` ranges (last takes the remainder), OpenMP over
 // ranges, serial sum of the partial results.
 template <class G, class Fr>
@@ -889,6 +1040,39 @@ struct Ops {
         store_point<G>((uint64_t *)out, r);
         return sec;
     }
+    // c != 0: every element followed by its multiples by 2^c (profile_multiexp.cpp:120-151)
+    static size_t stream_write(int form, const void *in, size_t n, size_t c, void *out) {
+        const size_t per = c ? (field_num_bits<Fr>() + c - 1) / c : 1;
+        std::vector<uint8_t> bytes;
+        for (size_t i = 0; i < n; i++) {
+            G el = load_point<G>((const uint64_t *)in + i * GW);
+            stream_put_point(bytes, el, form != 0);
+            for (size_t k = 1; k < per; k++) {
+                for (size_t j = 0; j < c; j++) el = el.dbl();
+                stream_put_point(bytes, el, form != 0);
+            }
+        }
+        if (out) memcpy(out, bytes.data(), bytes.size());
+        return bytes.size();
+    }
+    // multi_exp_stream (c == 0) / multi_exp_stream_with_precompute; 1 computed, 0 undefined in the
+    // reference (an empty bucket set is summed)
+    static int multi_exp_stream_(int form, const void *bytes, size_t nbytes, const void *scalars,
+                                 size_t n, size_t c, void *out, int normalize) {
+        const size_t per = c ? (field_num_bits<Fr>() + c - 1) / c : 1;
+        std::vector<G> el(n * per);
+        const uint8_t *in = (const uint8_t *)bytes;
+        if (nbytes != n * per * 2 * sizeof(G) / 3) return 0;
+        for (size_t i = 0; i < n * per; i++) in = stream_get_point(in, el[i], form != 0);
+        std::vector<Fr> s = load_scalars(scalars, n);
+        bool defined = true;
+        G r = c ? stream_precompute<G, Fr>(el.data(), s.data(), n, c, &defined)
+                : stream_all_rounds<G, Fr>(el.data(), s.data(), n, &defined);
+        if (!defined) return 0;
+        if (normalize) r.to_special();
+        store_point<G>((uint64_t *)out, r);
+        return 1;
+    }
     static void group_op(int op, const void *a, const void *b, void *out, size_t n) {
         for (size_t i = 0; i < n; i++) {
             G x = load_point<G>((const uint64_t *)a + i * GW), y = G::zero(), r;
@@ -1098,6 +1282,18 @@ double orc_multi_exp(int gid, int method, int form, const void *bases, const voi
     DISPATCH(gid, multi_exp_(method, form, bases, scalars, n, chunks, out, normalize));
     return -1.0;
 }
+size_t orc_stream_write(int gid, int form, const void *in, size_t n, size_t c, void *out) {
+    init_all();
+    DISPATCH(gid, stream_write(form, in, n, c, out));
+    return 0;
+}
+int orc_multi_exp_stream(int gid, int form, const void *bytes, size_t nbytes, const void *scalars,
+                         size_t n, size_t c, void *out, int normalize) {
+    init_all();
+    DISPATCH(gid, multi_exp_stream_(form, bytes, nbytes, scalars, n, c, out, normalize));
+    return -1;
+}
+size_t orc_bdlo12_signed_optimal_c(size_t n) { return pippenger_optimal_c(n) + 1; }
 void orc_batch_to_special(int gid, void *inout, size_t n) {
     init_all();
     switch (gid) {

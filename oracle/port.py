@@ -72,6 +72,9 @@ def lib():
             "orc_num_signed_digits": (sz, [i32, sz]),
             "orc_get_digit": (sz, [i32, vp, sz, sz]),
             "orc_pippenger_optimal_c": (sz, [sz]),
+            "orc_stream_write": (sz, [i32, i32, vp, sz, sz, vp]),
+            "orc_multi_exp_stream": (i32, [i32, i32, vp, sz, vp, sz, sz, vp, i32]),
+            "orc_bdlo12_signed_optimal_c": (sz, [sz]),
         }
         for name, (res, args) in sigs.items():
             f = getattr(L, name)
@@ -207,3 +210,33 @@ def num_signed_digits(fid, c) -> int:
 
 def pippenger_optimal_c(n) -> int:
     return int(lib().orc_pippenger_optimal_c(n))
+
+
+# ---- streamed / precomputed MSM (multiexp_stream.tcc:164-223), same shapes as oracle/ref.py ------
+FORM_PLAIN, FORM_MONTGOMERY = 0, 1
+
+
+def stream_write(gid, pts, form=FORM_MONTGOMERY, precompute_c=0) -> bytes:
+    a = _c(pts)
+    n = a.shape[0]
+    size = lib().orc_stream_write(gid, form, _p(a), n, precompute_c, None)
+    out = np.zeros(size, dtype=np.uint8)
+    lib().orc_stream_write(gid, form, _p(a), n, precompute_c, out.ctypes.data_as(C.c_void_p))
+    return out.tobytes()
+
+
+def multi_exp_stream(gid, data: bytes, scalars, form=FORM_MONTGOMERY, precompute_c=0,
+                     normalize=True):
+    """None where the reference sums an empty bucket set (undefined there, multiexp.tcc:88-106)."""
+    s = _c(scalars)
+    buf = np.frombuffer(data, dtype=np.uint8)
+    out = np.zeros(group_words(gid), dtype=np.uint64)
+    rc = lib().orc_multi_exp_stream(gid, form, buf.ctypes.data_as(C.c_void_p), len(data), _p(s),
+                                    s.shape[0], precompute_c, _p(out), int(normalize))
+    if rc < 0:
+        raise ValueError("orc_multi_exp_stream: unknown group")
+    return out if rc == 1 else None
+
+
+def bdlo12_signed_optimal_c(n) -> int:
+    return int(lib().orc_bdlo12_signed_optimal_c(n))

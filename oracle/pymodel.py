@@ -482,6 +482,16 @@ def wire_point(group: Group, P) -> bytes:
     return wire_coord(group, P[0]) + wire_coord(group, P[1])
 
 
+def stream_point(group: Group, P, montgomery: bool) -> bytes:
+    """libff's binary stream encoding of one element, uncompressed (curve_serialization.tcc:79-101,
+    field_serialization.tcc:127-147, 197-222): X then Y, extension coefficients lowest first, every
+    base-field value big-endian, either plain or its Montgomery representation; zero = (0, 1)."""
+    K, f = group.K, group.fq
+    x, y = (K.zero(), K.one()) if P is None else P
+    conv = f.to_mont if montgomery else (lambda v: v)
+    return b"".join(conv(c).to_bytes(f.nbytes, "big") for c in K.coeffs(x) + K.coeffs(y))
+
+
 def wire_scalar(group: Group, s: int) -> bytes:
     return int(s).to_bytes(group.fr.nbytes, "big")
 

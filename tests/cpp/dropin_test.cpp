@@ -10,7 +10,9 @@
 #include <libff/algebra/curves/bls12_381/bls12_381_pp.hpp>
 #include <libff/algebra/curves/bw6_761/bw6_761_pp.hpp>
 #include <libff/algebra/scalar_multiplication/multiexp.hpp>
+#include <libff/algebra/scalar_multiplication/multiexp_stream.hpp>
 #include <libff/common/rng.hpp>
+#include <sstream>
 
 #include "libff_b200.hpp"  // <- the only line a libff user adds
 
@@ -176,6 +178,52 @@ template<typename GroupT> void test_batch_exp(size_t n, size_t window)
     }
 }
 
+// multi_exp_stream / multi_exp_stream_with_precompute (multiexp_stream.tcc:164-223) on streams
+// written by the reference's own group_write, as profile_multiexp.cpp:100-151 does; expected
+// value from the CPU naive method
+template<typename GroupT, form_t Form, compression_t Comp> void test_stream(size_t n)
+{
+    using Field = typename GroupT::scalar_field;
+    std::vector<GroupT> bases;
+    std::vector<Field> scalars;
+    GroupT g = SHA512_rng<Field>(91) * GroupT::one();
+    const GroupT d = SHA512_rng<Field>(92) * GroupT::one();
+    for (size_t i = 0; i < n; ++i) {
+        bases.push_back(g);
+        g = g + d;
+        scalars.push_back(SHA512_rng<Field>(500 + i));
+    }
+    bases[n / 2] = GroupT::zero();
+    const GroupT expect = multi_exp<GroupT, Field, multi_exp_method_naive_plain>(
+        bases.begin(), bases.end(), scalars.begin(), scalars.end(), 1);
+    {
+        std::ostringstream os(std::ios_base::out | std::ios_base::binary);
+        for (const GroupT &el : bases) {
+            group_write<encoding_binary, Form, Comp>(el, os);
+        }
+        std::istringstream is(os.str(), std::ios_base::in | std::ios_base::binary);
+        const GroupT r = multi_exp_stream<Form, Comp, GroupT, Field>(is, scalars);
+        CHECK(expect == r);
+    }
+    {
+        const size_t c = bdlo12_signed_optimal_c(n);
+        const size_t per = (Field::num_bits + c - 1) / c;
+        std::ostringstream os(std::ios_base::out | std::ios_base::binary);
+        for (GroupT el : bases) {
+            group_write<encoding_binary, Form, Comp>(el, os);
+            for (size_t i = 0; i + 1 < per; ++i) {
+                for (size_t j = 0; j < c; ++j) {
+                    el = el.dbl();
+                }
+                group_write<encoding_binary, Form, Comp>(el, os);
+            }
+        }
+        std::istringstream is(os.str(), std::ios_base::in | std::ios_base::binary);
+        const GroupT r = multi_exp_stream_with_precompute<Form, Comp, GroupT, Field>(is, scalars, c);
+        CHECK(expect == r);
+    }
+}
+
 // TestEdgeCase1 (test_multiexp.cpp:344-390), literal vectors
 void test_edge_case1()
 {
@@ -243,6 +291,14 @@ int main()
         test_batch_exp<bls12_381_G2>(40, 4);
         test_batch_exp<bls12_377_G2>(40, 4);
         test_batch_exp<bw6_761_G2>(30, 4);
+        test_stream<alt_bn128_G1, form_montgomery, compression_off>(300);
+        test_stream<alt_bn128_G1, form_plain, compression_off>(100);
+        test_stream<alt_bn128_G1, form_plain, compression_on>(100);
+        test_stream<alt_bn128_G2, form_montgomery, compression_off>(60);
+        test_stream<bls12_377_G1, form_plain, compression_off>(80);
+        test_stream<bw6_761_G1, form_montgomery, compression_off>(40);
+        test_stream<bls12_381_G1, form_montgomery, compression_on>(60);
+        test_stream<bls12_381_G2, form_plain, compression_off>(40);
         test_edge_case1();
     } catch (const std::exception &e) {
         printf("EXCEPTION %s\n", e.what());

@@ -180,11 +180,40 @@ def main():
         out[f"wire/{gid}/point_bytes"] = np.frombuffer(ref.wire_group_write(gid, pts), dtype=np.uint8)
         out[f"wire/{gid}/scalars"] = sc
         out[f"wire/{gid}/scalar_bytes"] = np.frombuffer(ref.wire_scalar_write(gid, sc), dtype=np.uint8)
+    # ---- streamed / precomputed MSM and the binary stream encoding (multiexp_stream.tcc:164-223,
+    # curve_serialization.tcc:79-101).  "defined" = 0 where the reference sums an empty bucket set.
+    for gid in range(8):
+        G = pm.GROUPS[gid]
+        r = G.fr.p
+        zero, _ = ref.group_constants(gid)
+        P = ref.gen_bases_walk(gid, 24)
+        P[4] = zero
+        sc = ref.gen_scalars(gid, 24, start=4000)
+        sc[:6] = G.encode_scalars([0, 1, r - 1, r - 2, 1 << (r.bit_length() - 1), 2])
+        out[f"stream/{gid}/bases"] = P
+        out[f"stream/{gid}/scalars"] = sc
+        for form in (0, 1):
+            data = ref.stream_write(gid, P, form=form)
+            out[f"stream/{gid}/bytes_form{form}"] = np.frombuffer(data, dtype=np.uint8)
+            res = ref.multi_exp_stream(gid, data, sc, form=form, normalize=False)
+            out[f"stream/{gid}/defined_form{form}"] = np.array([res is not None], dtype=np.uint8)
+            if res is not None:
+                out[f"stream/{gid}/result_raw_form{form}"] = res
+        out[f"stream/{gid}/plain_msm"] = ref.multi_exp(gid, P, sc)
+        for c in (9, DIVIDING_C[gid]):
+            m = 3
+            data = ref.stream_write(gid, P[:m], form=1, precompute_c=c)
+            out[f"stream/{gid}/pre{c}_bytes"] = np.frombuffer(data, dtype=np.uint8)
+            res = ref.multi_exp_stream(gid, data, sc[1:1 + m], form=1, precompute_c=c, normalize=False)
+            out[f"stream/{gid}/pre{c}_result_raw"] = res
+            out[f"stream/{gid}/pre{c}_plain_msm"] = ref.multi_exp(gid, P[:m], sc[1:1 + m])
     np.savez_compressed(OUT, **out)
     print("wrote", OUT, os.path.getsize(OUT), "bytes,", len(out), "arrays")
 
 
 G_BITS = {0: 254, 1: 254, 2: 253, 3: 377, 4: 253, 5: 377, 6: 255, 7: 255}
+# digit sizes that divide the scalar width: the reference drops the carry out of the top digit
+DIVIDING_C = {0: 2, 1: 2, 2: 11, 3: 13, 4: 11, 5: 13, 6: 15, 7: 17}
 
 if __name__ == "__main__":
     main()

@@ -329,3 +329,60 @@ def test_wire_format_model_matches_reference_serializer(golden, gid):
     sc = g.decode_scalars(golden[f"wire/{gid}/scalars"])
     assert b"".join(pm.wire_scalar(g, s) for s in sc) == golden[f"wire/{gid}/scalar_bytes"].tobytes()
     assert len(want) // 4 == {0: 64, 1: 128, 2: 96, 3: 192, 4: 192, 5: 192, 6: 96, 7: 192}[gid]  # ffi/ffi.h:13-17,55-59 sizes
+
+
+# ------------------------------------------------------------------------------------------------
+# streamed / precomputed MSM (multiexp_stream.tcc:164-223) and the binary stream encoding
+
+DIVIDING_C = {0: 2, 1: 2, 2: 11, 3: 13, 4: 11, 5: 13, 6: 15, 7: 17}
+
+
+@pytest.mark.parametrize("gid", GROUPS)
+def test_stream_encoding_model_matches_reference_writer(golden, gid):
+    """group_write<encoding_binary, form, compression_off> (curve_serialization.tcc:79-101) against
+    the Python big-int model and the C++ restatement"""
+    g = pm.GROUPS[gid]
+    bases = golden[f"stream/{gid}/bases"]
+    pts = [g.decode(r) for r in bases]
+    assert pts[4] is None
+    for form in (0, 1):
+        want = golden[f"stream/{gid}/bytes_form{form}"].tobytes()
+        assert b"".join(pm.stream_point(g, P, bool(form)) for P in pts) == want
+        assert port.stream_write(gid, bases, form=form) == want
+    assert len(want) == len(pts) * 2 * g.coord_bytes
+
+
+@pytest.mark.parametrize("gid", GROUPS)
+def test_port_stream_msm_matches_reference(golden, gid):
+    """multi_exp_stream: the raw (non-normalised) representative of the restatement equals the
+    compiled reference's limb for limb, and both are the plain multi_exp element; where the
+    reference sums an empty bucket set (undefined there) the restatement says so too"""
+    sc = golden[f"stream/{gid}/scalars"]
+    for form in (0, 1):
+        data = golden[f"stream/{gid}/bytes_form{form}"].tobytes()
+        got = port.multi_exp_stream(gid, data, sc, form=form, normalize=False)
+        if golden[f"stream/{gid}/defined_form{form}"][0]:
+            np.testing.assert_array_equal(got, golden[f"stream/{gid}/result_raw_form{form}"])
+            np.testing.assert_array_equal(port.multi_exp_stream(gid, data, sc, form=form),
+                                          golden[f"stream/{gid}/plain_msm"])
+        else:
+            assert got is None
+    # 24 points, c = 8: 377-bit scalars leave the top digit position empty, 253..255-bit ones do not
+    assert bool(golden[f"stream/{gid}/defined_form1"][0]) == (gid not in (3, 5))
+
+
+@pytest.mark.parametrize("gid", GROUPS)
+def test_port_precomputed_stream_msm_matches_reference(golden, gid):
+    """multi_exp_stream_with_precompute on the reference's own precompute stream (each base followed
+    by its multiples).  For a digit size dividing the scalar width the reference drops the carry
+    out of the top digit of r - 1 and r - 2 (field_utils.tcc:205-239): pinned here as the
+    reference's behaviour; the engine folds such scalars and returns the true sum."""
+    sc = golden[f"stream/{gid}/scalars"][1:4]  # 1, r - 1, r - 2
+    for c in (9, DIVIDING_C[gid]):
+        data = golden[f"stream/{gid}/pre{c}_bytes"].tobytes()
+        assert port.stream_write(gid, golden[f"stream/{gid}/bases"][:3], form=1, precompute_c=c) == data
+        got = port.multi_exp_stream(gid, data, sc, form=1, precompute_c=c, normalize=False)
+        np.testing.assert_array_equal(got, golden[f"stream/{gid}/pre{c}_result_raw"])
+        norm = port.multi_exp_stream(gid, data, sc, form=1, precompute_c=c)
+        same = np.array_equal(norm, golden[f"stream/{gid}/pre{c}_plain_msm"])
+        assert same == (c != DIVIDING_C[gid])
