@@ -937,6 +937,10 @@ bool b200msm_set_option(const char *name, int64_t value) {
     if (!g_ctx) return set_error("set_option before init"), false;
     if (name && !strcmp(name, "window_bits")) return g_ctx->opt_window_bits = (int)value, true;
     if (name && !strcmp(name, "segment")) return g_ctx->opt_segment = (int)value, true;
+    if (name && !strcmp(name, "carry_segment")) {
+        if (value < 0 || value > 1024) return set_error("carry_segment out of range"), false;
+        return g_ctx->opt_carry_segment = (int)value, true;
+    }
     if (name && !strcmp(name, "reduce_chunk")) return g_ctx->opt_reduce_chunk = (int)value, true;
     if (name && !strcmp(name, "h2d_growth")) {
         if (value < 0 || value > 400) return set_error("h2d_growth out of range (percent)"), false;

@@ -43,6 +43,7 @@ enum Slot {
     SL_INF,         // infinity flags
     SL_SCALARS,     // uploaded scalars
     SL_DIGITS,
+    SL_RANKS,       // rank of every item inside its bucket (the histogram counter it saw)
     SL_HIST,
     SL_OFFSETS,
     SL_CURSOR,
@@ -101,6 +102,7 @@ struct Ctx {
     int opt_segment = 0;      // 0 = default
     int opt_h2d_parts = 0;    // 0 = automatic
     int opt_h2d_growth = 0;   // size ratio of consecutive ranges in percent; 0 = default (130)
+    int opt_carry_segment = 0; // carries per thread in the later accumulation rounds; 0 = automatic
     int opt_reduce_chunk = 0; // log2 of the buckets per thread in the reduction; 0 = automatic
 
     bool reserve(Slot s, size_t bytes, void **out);

@@ -128,7 +128,16 @@ bool sum_impl(Ctx &ctx, const void *d_raw, size_t count, void *d_out) {
 }
 
 // ------------------------------------------------------------------------------------------
-constexpr int SEG_CARRY = 16;   // carries per thread, later accumulation rounds
+// Carries per thread in the later accumulation rounds.  Every thread walks its carries serially
+// with full additions (14 field products each): long segments need fewer rounds, short ones keep
+// the serial chain of the wide fields (microseconds per product) short.
+template <class C>
+inline uint32_t pick_carry_segment(const Ctx &ctx) {
+    if (ctx.opt_carry_segment > 0) return (uint32_t)ctx.opt_carry_segment;
+    constexpr int words = Raw<C>::CW;  // 32-bit words per coordinate
+    (void)words;
+    return 4u;  // measured best (or equal) for 8-, 12-, 16- and 24-word coordinates
+}
 
 // Sorted entries per thread in the first accumulation round: long segments amortise the carry
 // rounds (one full addition per segment), short ones keep all SMs busy on small inputs.
@@ -169,18 +178,19 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
         return false;
     }
     int32_t *digits;
-    uint32_t *hist, *offsets, *cursor, *buckets, *chunks, *windows;
+    uint32_t *hist, *offsets, *buckets, *chunks, *windows;
     Entry *sorted;
     if (!reserve_as(ctx, SL_DIGITS, (size_t)W * n * 4, &digits)) return false;
     if (!reserve_as(ctx, SL_HIST, M * 4, &hist)) return false;
     if (!reserve_as(ctx, SL_OFFSETS, (M + 2) * 4, &offsets)) return false;  // + total, used windows
-    if (!reserve_as(ctx, SL_CURSOR, M * 4, &cursor)) return false;
     if (!reserve_as(ctx, SL_BUCKETS, M * R::XW * 4, &buckets)) return false;
 
     // --- digits + histogram
     B200_CUDA(cudaMemsetAsync(hist, 0, M * 4, st));
     B200_CUDA(cudaMemsetAsync(offsets + M + 1, 0, 4, st));
-    k_digits<C><<<cdiv(n, 256), 256, 0, st>>>((const uint32_t *)d_scalars, d_inf, digits, hist,
+    uint32_t *ranks;
+    if (!reserve_as(ctx, SL_RANKS, (size_t)W * n * 4, &ranks)) return false;
+    k_digits<C><<<cdiv(n, 256), 256, 0, st>>>((const uint32_t *)d_scalars, d_inf, digits, ranks, hist,
                                                offsets + M + 1, (uint32_t)n, c, W, bstride, fold_bit);
     B200_LAUNCH_CHECK(ctx);
     B200_CUDA(cudaEventRecord(ctx.ev[PH_DIGITS + 1], st));
@@ -192,7 +202,7 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
     B200_LAUNCH_CHECK(ctx);
     k_scan_tile_sums<<<1, 1024, 0, st>>>(tile_sums, tiles);
     B200_LAUNCH_CHECK(ctx);
-    k_scan_apply<<<tiles, SCAN_THREADS, 0, st>>>(hist, tile_sums, tiles, offsets, cursor, (uint32_t)M);
+    k_scan_apply<<<tiles, SCAN_THREADS, 0, st>>>(hist, tile_sums, tiles, offsets, (uint32_t)M);
     B200_LAUNCH_CHECK(ctx);
     B200_CUDA(cudaEventRecord(ctx.ev[PH_SCAN + 1], st));
     // the number of sorted items is known after the scan; it sizes the accumulation segments
@@ -209,7 +219,7 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
     // the sorted array is read four items at a time
     if (!reserve_as(ctx, SL_SORTED, ((size_t)W * n + 4) * sizeof(Entry), &sorted)) return false;
     // --- scatter
-    k_scatter<C><<<dim3(cdiv(n, 256), W), 256, 0, st>>>(digits, cursor, sorted, seg_bucket,
+    k_scatter<C><<<dim3(cdiv(n, 256), W), 256, 0, st>>>(digits, ranks, offsets, sorted, seg_bucket,
                                                        (uint32_t)n, seg, bstride,
                                                        pre ? shape->pstride : 1u,
                                                        pre ? shape->wstride : 0u);
@@ -218,6 +228,7 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
 
     // --- accumulation rounds
     if (total > 0) {
+        const uint32_t SEG_CARRY = pick_carry_segment<C>(ctx);
         size_t t2 = (t1 + SEG_CARRY - 1) / SEG_CARRY;
         uint32_t *keyA, *ptA, *keyB, *ptB;
         if (!reserve_as(ctx, SL_CARRY_KEY_A, t1 * 4, &keyA)) return false;

@@ -5,7 +5,8 @@
 //   k_digits        scalars: Montgomery -> plain (fp.tcc:270-281) -> signed c-bit digits
 //                   (field_utils.tcc:167-239 restated as a single carry pass) + bucket histogram
 //   k_scan_*        exclusive prefix sum of the histogram -> bucket offsets (3 launches)
-//   k_scatter       counting-sort scatter of (point index | sign) words; also records the bucket
+//   k_scatter       counting-sort scatter of (point index | sign) words to offsets[bucket] + the
+//                   rank the histogram pass handed out (no atomics); also records the bucket
 //                   that owns the first item of every accumulation segment
 //   k_accum_first   balanced segmented accumulation: every thread sums SEG consecutive sorted
 //                   entries with mixed additions (multiexp.tcc:319-345 / :45-81); sums of buckets
@@ -73,9 +74,9 @@ __device__ __forceinline__ uint32_t warp_cursor_take(uint32_t *cursor, bool vali
 // by r - s, whose top digit is small, and all its digits change sign: s P = -(r - s) P.
 template <class C>
 __global__ void k_digits(const uint32_t *__restrict__ scalars, const uint8_t *__restrict__ inf_flag,
-                         int32_t *__restrict__ digits, uint32_t *__restrict__ hist,
-                         uint32_t *__restrict__ used_windows, uint32_t n, int c, int W,
-                         uint32_t bstride, int fold_bit) {
+                         int32_t *__restrict__ digits, uint32_t *__restrict__ ranks,
+                         uint32_t *__restrict__ hist, uint32_t *__restrict__ used_windows,
+                         uint32_t n, int c, int W, uint32_t bstride, int fold_bit) {
     using Fr = typename C::Fr;
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t top = 0;  // 1 + index of the highest window with a non-zero digit
@@ -102,7 +103,11 @@ __global__ void k_digits(const uint32_t *__restrict__ scalars, const uint8_t *__
             if (skip) sd = 0;
             if (live) digits[(size_t)w * n + i] = sd;
             if (sd != 0) top = w + 1;
-            warp_hist_add(hist, sd != 0, (uint32_t)w * bstride + (uint32_t)(sd < 0 ? -sd : sd) - 1);
+            // the counter's value before this item = the item's rank inside its bucket: the
+            // scatter then needs no second round of atomics
+            const uint32_t rank = warp_cursor_take(
+                hist, sd != 0, (uint32_t)w * bstride + (uint32_t)(sd < 0 ? -sd : sd) - 1);
+            if (live) ranks[(size_t)w * n + i] = rank;
 #pragma unroll
             for (int k = 0; k < Fr::N - 1; k++) s.v[k] = __funnelshift_r(s.v[k], s.v[k + 1], c);
             s.v[Fr::N - 1] >>= c;
@@ -116,7 +121,7 @@ __global__ void k_digits(const uint32_t *__restrict__ scalars, const uint8_t *__
 
 // ------------------------------------------------------------------------------------------
 // Exclusive scan of the m bucket counters in three launches: per-tile sums, scan of the tile
-// sums (one block), per-tile scan + tile offset.  offsets has m + 1 entries, cursor m.
+// sums (one block), per-tile scan + tile offset.  offsets has m + 1 entries.
 constexpr int SCAN_THREADS = 256;
 constexpr int SCAN_ITEMS = 8;                          // counters per thread
 constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;   // counters per block
@@ -179,8 +184,7 @@ static __global__ void __launch_bounds__(1024)
 
 static __global__ void __launch_bounds__(SCAN_THREADS)
     k_scan_apply(const uint32_t *__restrict__ hist, const uint32_t *__restrict__ tile_sums,
-                 uint32_t tiles, uint32_t *__restrict__ offsets, uint32_t *__restrict__ cursor,
-                 uint32_t m) {
+                 uint32_t tiles, uint32_t *__restrict__ offsets, uint32_t m) {
     __shared__ uint32_t ws[33];
     const uint32_t base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
     uint32_t v[SCAN_ITEMS], s = 0;
@@ -195,7 +199,6 @@ static __global__ void __launch_bounds__(SCAN_THREADS)
     for (int j = 0; j < SCAN_ITEMS; j++) {
         if (base + j < m) {
             offsets[base + j] = run;
-            cursor[base + j] = run;
         }
         run += v[j];
     }
@@ -206,16 +209,16 @@ static __global__ void __launch_bounds__(SCAN_THREADS)
 // item = index of the point to add: i for the plain MSM (pstride 1, wstride 0); the position of
 // 2^(w c) P_i in a precomputed table otherwise (i * pstride + w * wstride).
 template <class C>
-__global__ void k_scatter(const int32_t *__restrict__ digits, uint32_t *__restrict__ cursor,
-                          Entry *__restrict__ sorted, uint32_t *__restrict__ seg_bucket,
-                          uint32_t n, uint32_t SEG, uint32_t bstride, uint32_t pstride,
-                          uint32_t wstride) {
+__global__ void k_scatter(const int32_t *__restrict__ digits, const uint32_t *__restrict__ ranks,
+                          const uint32_t *__restrict__ offsets, Entry *__restrict__ sorted,
+                          uint32_t *__restrict__ seg_bucket, uint32_t n, uint32_t SEG,
+                          uint32_t bstride, uint32_t pstride, uint32_t wstride) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t w = blockIdx.y;
     const int32_t d = i < n ? digits[(size_t)w * n + i] : 0;
-    const uint32_t b = w * bstride + (uint32_t)(d < 0 ? -d : d) - 1;
-    const uint32_t pos = warp_cursor_take(cursor, d != 0, b);  // all lanes take part
     if (d == 0) return;
+    const uint32_t b = w * bstride + (uint32_t)(d < 0 ? -d : d) - 1;
+    const uint32_t pos = offsets[b] + ranks[(size_t)w * n + i];
     sorted[pos] = (i * pstride + w * wstride) | (d < 0 ? 0x80000000u : 0u);
     // every position is written exactly once, so exactly one thread sees each segment start
     if (pos % SEG == 0) seg_bucket[pos / SEG] = b;
