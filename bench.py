@@ -40,8 +40,9 @@ MUL_MACS = {0: 136, 1: 136, 2: 300, 3: 1176, 4: 300, 5: 1176, 6: 300, 7: 300}
 MIN_BYTES = {0: 96, 1: 160, 2: 128, 3: 240, 4: 224, 5: 240, 6: 128, 7: 224}
 
 
-# ncu --set full, k_accum_first, per launch: 28.14 GB read + 1.26 GB written
-NCU_TRAFFIC = {("alt_bn128_g1", 1 << 24): 29.40e9}
+# ncu --set full, k_accum_first, per launch: 28.72 GB read + 1.28 GB written
+# (profiles/accum_first_r01d_raw.csv)
+NCU_TRAFFIC = {("alt_bn128_g1", 1 << 24): 30.00e9}
 
 
 def ceil_log2(n):
@@ -298,7 +299,7 @@ def main():
                             f"L={MUL_MACS[gid]}, c_ref={c_ref}) x 2 IMAD slots",
         "kernel_ms": accum_ms, "kernel_share_of_step": accum_ms / phase_ms["total"],
         # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the committed
-        # `ncu --set full` capture of this workload (profiles/accum_first_r01b_raw.csv)
+        # `ncu --set full` capture of this workload (profiles/accum_first_r01d_raw.csv)
         "traffic": NCU_TRAFFIC.get((args.group, n)),
         "traffic_unit": "bytes per launch (ncu dram read + write); algorithmic gather = items x "
                         "(affine point + 4-byte item)",
