@@ -171,7 +171,11 @@ bool b200msm_stream_finish(uint64_t stream, void *out, size_t out_bytes);
 /* Tuning and measurement (not part of the reference surface).
  * option: "window_bits" (0 = automatic), "segment" (entries per thread of the accumulation),
  * "h2d_parts" (point ranges a host-buffer multi_exp is cut into so that uploads overlap the
- * computation; 0 = automatic, 1 = no overlap). */
+ * computation; 0 = automatic, 1 = no overlap), "h2d_growth" (size ratio of consecutive ranges in
+ * percent; 0 = 130), "window_groups" (groups the windows are walked in, top window first, so that
+ * the reduction of one group runs under the accumulation of the next; 0 = automatic, 1 = one
+ * group), "carry_segment" (carries per thread in the later accumulation rounds; 0 = 4),
+ * "reduce_chunk" (log2 of the buckets per thread in the bucket reduction; 0 = automatic). */
 bool b200msm_set_option(const char *name, int64_t value);
 /* CUDA-event timings (ms) of the phases of the most recent multi_exp on this thread's engine,
  * measured on the engine's own stream.  Writes up to `cap` values, returns how many phases exist.

@@ -306,6 +306,9 @@ bool b200msm_init(int device) {
     int prio_lo = 0, prio_hi = 0;
     B200_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
     B200_CUDA(cudaStreamCreateWithPriority(&ctx->tail_stream, cudaStreamNonBlocking, prio_hi));
+    B200_CUDA(cudaStreamCreateWithFlags(&ctx->acc_stream, cudaStreamNonBlocking));
+    B200_CUDA(cudaEventCreateWithFlags(&ctx->ev_group_go, cudaEventDisableTiming));
+    for (auto &e : ctx->ev_group) B200_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     for (auto &e : ctx->ev_timer) B200_CUDA(cudaEventCreate(&e));
     B200_CUDA(cudaEventCreateWithFlags(&ctx->ev_tail_go, cudaEventDisableTiming));
     B200_CUDA(cudaEventCreateWithFlags(&ctx->ev_tail_done, cudaEventDisableTiming));
@@ -317,7 +320,7 @@ void b200msm_shutdown(void) {
     std::lock_guard<std::mutex> lk(g_mutex);
     if (!g_ctx) return;
     cudaSetDevice(g_ctx->device);
-    cudaStreamSynchronize(g_ctx->stream);
+    cudaDeviceSynchronize();
     for (auto &kv : g_resident) {
         cudaFree(kv.second.data);
         if (kv.second.inf) cudaFree(kv.second.inf);
@@ -338,6 +341,9 @@ void b200msm_shutdown(void) {
     cudaEventDestroy(g_ctx->ev_tail_go);
     cudaEventDestroy(g_ctx->ev_tail_done);
     cudaStreamDestroy(g_ctx->tail_stream);
+    cudaStreamDestroy(g_ctx->acc_stream);
+    cudaEventDestroy(g_ctx->ev_group_go);
+    for (auto &e : g_ctx->ev_group) cudaEventDestroy(e);
     cudaStreamDestroy(g_ctx->copy_stream);
     cudaStreamDestroy(g_ctx->stream);
     delete g_ctx;
@@ -937,6 +943,10 @@ bool b200msm_set_option(const char *name, int64_t value) {
     if (!g_ctx) return set_error("set_option before init"), false;
     if (name && !strcmp(name, "window_bits")) return g_ctx->opt_window_bits = (int)value, true;
     if (name && !strcmp(name, "segment")) return g_ctx->opt_segment = (int)value, true;
+    if (name && !strcmp(name, "window_groups")) {
+        if (value < 0 || value > 64) return set_error("window_groups out of range"), false;
+        return g_ctx->opt_window_groups = (int)value, true;
+    }
     if (name && !strcmp(name, "carry_segment")) {
         if (value < 0 || value > 1024) return set_error("carry_segment out of range"), false;
         return g_ctx->opt_carry_segment = (int)value, true;

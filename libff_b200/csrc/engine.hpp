@@ -55,6 +55,9 @@ enum Slot {
     SL_CARRY_PT_A,
     SL_CARRY_KEY_B,
     SL_CARRY_PT_B,
+    SL_CARRY_KEY_C,
+    SL_CARRY_PT_C,
+    SL_HORNER,      // running value of the Horner chain between window groups
     SL_CHUNKS,
     SL_CHUNK_TOTALS,
     SL_WINDOWS,
@@ -89,6 +92,10 @@ struct Ctx {
     // under the next range's digit/scatter/accumulation kernels.
     cudaStream_t tail_stream = nullptr;
     cudaEvent_t ev_tail_go = nullptr, ev_tail_done = nullptr;
+    // window groups of one MSM: consecutive accumulations alternate between `stream` and
+    // `acc_stream`, the reductions that follow each of them go to `tail_stream`
+    cudaStream_t acc_stream = nullptr;
+    cudaEvent_t ev_group_go = nullptr, ev_group[2] = {};
     bool defer_tail = false;    // set by the pipelined caller
     bool tail_pending = false;  // a deferred tail may still be reading the reduction scratch
     void *slot_ptr[SL_COUNT] = {};
@@ -102,6 +109,7 @@ struct Ctx {
     int opt_segment = 0;      // 0 = default
     int opt_h2d_parts = 0;    // 0 = automatic
     int opt_h2d_growth = 0;   // size ratio of consecutive ranges in percent; 0 = default (130)
+    int opt_window_groups = 0; // groups the windows are walked in (top-down); 0 = automatic, 1 = one
     int opt_carry_segment = 0; // carries per thread in the later accumulation rounds; 0 = automatic
     int opt_reduce_chunk = 0; // log2 of the buckets per thread in the reduction; 0 = automatic
 

@@ -205,9 +205,14 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
     k_scan_apply<<<tiles, SCAN_THREADS, 0, st>>>(hist, tile_sums, tiles, offsets, (uint32_t)M);
     B200_LAUNCH_CHECK(ctx);
     B200_CUDA(cudaEventRecord(ctx.ev[PH_SCAN + 1], st));
-    // the number of sorted items is known after the scan; it sizes the accumulation segments
+    // the number of sorted items is known after the scan; it sizes the accumulation segments.
+    // Also read back: the first sorted position of every window (offsets[w * B], one strided copy).
     uint32_t meta[2] = {0, 0};
+    std::vector<uint32_t> wpos((size_t)W + 1, 0);
     B200_CUDA(cudaMemcpyAsync(meta, offsets + M, 8, cudaMemcpyDeviceToHost, st));
+    if (!pre)
+        B200_CUDA(cudaMemcpy2DAsync(wpos.data(), 4, offsets, (size_t)B * 4, 4, (size_t)W + 1,
+                                    cudaMemcpyDeviceToHost, st));
     B200_CUDA(cudaStreamSynchronize(st));
     const uint32_t total = meta[0];
     // windows (bucket sets) that hold items
@@ -226,36 +231,7 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
     B200_LAUNCH_CHECK(ctx);
     B200_CUDA(cudaEventRecord(ctx.ev[PH_SCATTER + 1], st));
 
-    // --- accumulation rounds
-    if (total > 0) {
-        const uint32_t SEG_CARRY = pick_carry_segment<C>(ctx);
-        size_t t2 = (t1 + SEG_CARRY - 1) / SEG_CARRY;
-        uint32_t *keyA, *ptA, *keyB, *ptB;
-        if (!reserve_as(ctx, SL_CARRY_KEY_A, t1 * 4, &keyA)) return false;
-        if (!reserve_as(ctx, SL_CARRY_PT_A, t1 * R::XW * 4, &ptA)) return false;
-        if (!reserve_as(ctx, SL_CARRY_KEY_B, t2 * 4, &keyB)) return false;
-        if (!reserve_as(ctx, SL_CARRY_PT_B, t2 * R::XW * 4, &ptB)) return false;
-        k_accum_first<C><<<cdiv(t1, 128), 128, 0, st>>>(sorted, offsets, seg_bucket, total, seg,
-                                                        (const uint32_t *)d_aff, buckets, keyA, ptA);
-        B200_LAUNCH_CHECK(ctx);
-        B200_CUDA(cudaEventRecord(ctx.ev[PH_ACCUM + 1], st));
-        size_t len = t1;
-        while (true) {
-            size_t tn = (len + SEG_CARRY - 1) / SEG_CARRY;
-            k_accum_carry<C><<<cdiv(tn, 128), 128, 0, st>>>(keyA, ptA, (uint32_t)len, SEG_CARRY,
-                                                            buckets, keyB, ptB);
-            B200_LAUNCH_CHECK(ctx);
-            if (tn == 1) break;  // a single thread owns every run it sees: no carries remain
-            std::swap(keyA, keyB);
-            std::swap(ptA, ptB);
-            len = tn;
-        }
-    } else {
-        B200_CUDA(cudaEventRecord(ctx.ev[PH_ACCUM + 1], st));
-    }
-    B200_CUDA(cudaEventRecord(ctx.ev[PH_CARRY + 1], st));
-
-    // --- bucket reduction (Br and K are powers of two, K <= Br).  A single bucket set
+    // --- reduction geometry (Br and K are powers of two, K <= Br).  A single bucket set
     // (precomputed multiples) is cut into V slices that go through the reduction like V windows.
     const uint32_t V = pre ? (B >= 4096 ? 16u : 1u) : 1u;
     const uint32_t Br = B / V;
@@ -268,18 +244,12 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
     uint32_t log2K = 0, log2Br = 0;
     while ((1u << log2K) < K) log2K++;
     while ((1u << log2Br) < Br) log2Br++;
-    uint32_t *chunk_T, *window_T = nullptr;
+    uint32_t *chunk_T, *window_T = nullptr, *horner;
     if (!reserve_as(ctx, SL_CHUNKS, (size_t)Wr * nchunks * R::XW * 4, &chunks)) return false;
     if (!reserve_as(ctx, SL_CHUNK_TOTALS, (size_t)Wr * nchunks * R::XW * 4, &chunk_T)) return false;
     if (!reserve_as(ctx, SL_WINDOWS, (size_t)2 * Wr * R::XW * 4, &windows)) return false;
+    if (!reserve_as(ctx, SL_HORNER, (size_t)R::XW * 4, &horner)) return false;
     if (pre) window_T = windows + (size_t)Wr * R::XW;
-    if (ctx.tail_pending) {  // the previous range's tail reads chunks / chunk_T / windows
-        B200_CUDA(cudaStreamWaitEvent(st, ctx.ev_tail_done, 0));
-        ctx.tail_pending = false;
-    }
-    k_bucket_reduce<C><<<dim3(cdiv(nchunks, 64), Wr), 64, 0, st>>>(buckets, hist, Br, K, chunks, chunk_T);
-    B200_LAUNCH_CHECK(ctx);
-    B200_CUDA(cudaEventRecord(ctx.ev[PH_BUCKET_REDUCE + 1], st));
     constexpr int WR_THREADS = 256;
     const size_t wr_smem = (size_t)WR_THREADS * R::XW * 4;
     static bool attr_set = false;
@@ -288,23 +258,153 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wr_smem));
         attr_set = true;
     }
-    cudaStream_t ts = st;
-    if (ctx.defer_tail) {
-        ts = ctx.tail_stream;
-        B200_CUDA(cudaEventRecord(ctx.ev_tail_go, st));
-        B200_CUDA(cudaStreamWaitEvent(ts, ctx.ev_tail_go, 0));
+    if (ctx.tail_pending) {  // the previous range's tail reads chunks / chunk_T / windows
+        B200_CUDA(cudaStreamWaitEvent(st, ctx.ev_tail_done, 0));
+        ctx.tail_pending = false;
     }
-    k_window_reduce<C, WR_THREADS><<<Wr, WR_THREADS, wr_smem, ts>>>(chunks, chunk_T, nchunks, log2K,
-                                                                   windows, window_T);
-    B200_LAUNCH_CHECK(ctx);
-    if (pre)
-        k_final_slices<C><<<1, 32, 0, ts>>>(windows, window_T, (int)V, (int)log2Br, (uint32_t *)d_out);
-    else
-        k_final<C><<<1, 32, 0, ts>>>(windows, Wu, c, (uint32_t *)d_out);
-    B200_LAUNCH_CHECK(ctx);
-    if (ctx.defer_tail) {
+
+    // --- groups of windows, walked from the top window down.  The accumulation of a group is one
+    // launch of k_accum_first over the group's segments; everything after it -- carry rounds,
+    // bucket reduction, window totals, the group's stretch of the Horner chain -- is a string of
+    // small or latency-bound kernels that runs on the high-priority side stream UNDER the
+    // accumulation of the next group.  Only the bottom group's string (one window) is exposed.
+    // Consecutive accumulations alternate between two streams so that the last, partly filled
+    // wave of one launch overlaps the first wave of the next.
+    struct Group {
+        int lo, hi;  // windows [lo, hi)
+    };
+    std::vector<Group> groups;  // top-down
+    if (pre || total == 0) {
+        groups.push_back(Group{0, Wr});
+    } else {
+        int ng = ctx.opt_window_groups;
+        std::vector<int> sizes;  // bottom-up
+        // Measured (profiles/groups_sweep_r01d.log): more than one group does not pay.  The strings
+        // of small kernels are chains of dependent field products; next to an accumulation that
+        // saturates the multiply pipe of every SM their warps wait for issue slots and the chains
+        // stretch more than the overlap hides (2^24 alt_bn128 G1: 42.5 ms with one group, 48.6 with
+        // six; bw6_761 2^19: 50 against 95 ms).  The default is therefore ONE group; the option
+        // stays for experiments (an SM partition reserved for the side stream would change this).
+        if (ng == 0) ng = 1;
+        if (ng == 1 || Wu == 1) {
+            sizes.push_back(Wu);
+        } else if (ng > 1 && ng < 64) {
+            for (int g = 0; g < std::min(ng, Wu); g++) sizes.push_back(0);
+            for (int w = 0; w < Wu; w++) sizes[(size_t)w * sizes.size() / Wu]++;
+        } else {  // 64: 1, 1, 2, then threes (bottom-up)
+            int left = Wu;
+            for (int want : {1, 1, 2}) {
+                if (left <= 0) break;
+                sizes.push_back(std::min(want, left));
+                left -= sizes.back();
+            }
+            while (left > 0) {
+                sizes.push_back(std::min(3, left));
+                left -= sizes.back();
+            }
+        }
+        int hi = Wu;
+        for (size_t g = sizes.size(); g-- > 0;) {
+            groups.push_back(Group{hi - sizes[g], hi});
+            hi -= sizes[g];
+        }
+    }
+    const size_t G = groups.size();
+    const bool side = G > 1 || ctx.defer_tail;      // tails on the side stream
+    cudaStream_t ts = side ? ctx.tail_stream : st;
+    const uint32_t SEG_CARRY = pick_carry_segment<C>(ctx);
+    uint32_t *keyA = nullptr, *ptA = nullptr, *keyB = nullptr, *ptB = nullptr, *keyC = nullptr, *ptC = nullptr;
+    if (total > 0) {
+        const size_t t2 = (t1 + 1 + SEG_CARRY - 1) / SEG_CARRY, t3 = (t2 + SEG_CARRY - 1) / SEG_CARRY;
+        if (!reserve_as(ctx, SL_CARRY_KEY_A, t1 * 4, &keyA)) return false;
+        if (!reserve_as(ctx, SL_CARRY_PT_A, t1 * R::XW * 4, &ptA)) return false;
+        if (!reserve_as(ctx, SL_CARRY_KEY_B, t2 * 4, &keyB)) return false;
+        if (!reserve_as(ctx, SL_CARRY_PT_B, t2 * R::XW * 4, &ptB)) return false;
+        if (!reserve_as(ctx, SL_CARRY_KEY_C, t3 * 4, &keyC)) return false;
+        if (!reserve_as(ctx, SL_CARRY_PT_C, t3 * R::XW * 4, &ptC)) return false;
+    }
+    if (G > 1) {
+        B200_CUDA(cudaEventRecord(ctx.ev_group_go, st));
+        B200_CUDA(cudaStreamWaitEvent(ctx.acc_stream, ctx.ev_group_go, 0));
+    }
+    // segment that holds the first item of window w (the segment straddling two windows belongs
+    // to the upper one)
+    auto seg_of_window = [&](int w) -> uint32_t { return w <= 0 ? 0u : wpos[(size_t)w] / seg; };
+    for (size_t g = 0; g < G; g++) {
+        const Group &gr = groups[g];
+        const bool first = g == 0, last = g + 1 == G;
+        cudaStream_t as = (g & 1) ? ctx.acc_stream : st;
+        if (total > 0) {
+            const uint32_t tb = (pre || last) ? 0u : seg_of_window(gr.lo);
+            const uint32_t te = (pre || first) ? (uint32_t)t1 : seg_of_window(gr.hi);
+            if (te > tb) {
+                k_accum_first<C><<<cdiv(te - tb, 128), 128, 0, as>>>(
+                    sorted, offsets, seg_bucket, total, seg, tb, te, (const uint32_t *)d_aff, buckets,
+                    keyA, ptA);
+                B200_LAUNCH_CHECK(ctx);
+            }
+            if (side) {
+                B200_CUDA(cudaEventRecord(ctx.ev_group[g & 1], as));
+                B200_CUDA(cudaStreamWaitEvent(ts, ctx.ev_group[g & 1], 0));
+            }
+            if (last) B200_CUDA(cudaEventRecord(ctx.ev[PH_ACCUM + 1], as));
+            // carry rounds over entries [tb, te] (both boundary entries; each is live in one group)
+            const uint32_t cb = tb, ce = std::min<uint32_t>((uint32_t)t1, te + 1);
+            const uint32_t key_lo = pre ? 0u : (uint32_t)gr.lo * B;
+            const uint32_t key_hi = pre ? CARRY_DEAD : (uint32_t)gr.hi * B;
+            const uint32_t *kin = keyA, *pin = ptA;
+            uint32_t *kout = keyB, *pout = ptB;
+            uint32_t begin = cb, endp = ce;
+            while (endp > begin) {
+                const size_t tn = ((size_t)(endp - begin) + SEG_CARRY - 1) / SEG_CARRY;
+                k_accum_carry<C><<<cdiv(tn, 128), 128, 0, ts>>>(kin, pin, begin, endp, key_lo, key_hi,
+                                                                SEG_CARRY, buckets, kout, pout);
+                B200_LAUNCH_CHECK(ctx);
+                if (tn == 1) break;  // a single thread owns every run it sees: no carries remain
+                kin = kout, pin = pout;
+                kout = (kout == keyB) ? keyC : keyB;
+                pout = (pout == ptB) ? ptC : ptB;
+                begin = 0, endp = (uint32_t)tn;
+            }
+        } else if (last) {
+            B200_CUDA(cudaEventRecord(ctx.ev[PH_ACCUM + 1], st));
+        }
+        if (!side) B200_CUDA(cudaEventRecord(ctx.ev[PH_CARRY + 1], st));
+        // bucket reduction, window totals, Horner stretch of this group
+        k_bucket_reduce<C><<<dim3(cdiv(nchunks, 64), gr.hi - gr.lo), 64, 0, ts>>>(
+            buckets, hist, Br, K, (uint32_t)gr.lo, chunks, chunk_T);
+        B200_LAUNCH_CHECK(ctx);
+        if (!side) B200_CUDA(cudaEventRecord(ctx.ev[PH_BUCKET_REDUCE + 1], st));
+        if (last && ctx.defer_tail) {
+            // the next range's digit pass rewrites hist / buckets: it may start from here on
+            B200_CUDA(cudaEventRecord(ctx.ev_tail_go, ts));
+            B200_CUDA(cudaStreamWaitEvent(st, ctx.ev_tail_go, 0));
+        }
+        k_window_reduce<C, WR_THREADS><<<gr.hi - gr.lo, WR_THREADS, wr_smem, ts>>>(
+            chunks, chunk_T, nchunks, log2K, (uint32_t)gr.lo, windows, window_T);
+        B200_LAUNCH_CHECK(ctx);
+        if (pre)
+            k_final_slices<C><<<1, 32, 0, ts>>>(windows, window_T, (int)V, (int)log2Br, (uint32_t *)d_out);
+        else
+            k_final<C><<<1, 32, 0, ts>>>(windows, gr.lo, gr.hi, c, horner, first, last, (uint32_t *)d_out);
+        B200_LAUNCH_CHECK(ctx);
+    }
+    if (G > 1 && (G & 1) == 0) {
+        // the last accumulation ran on the second stream: the caller's stream must see it
+        // (ev_group[1] was recorded after it)
+        B200_CUDA(cudaStreamWaitEvent(st, ctx.ev_group[1], 0));
+    }
+    if (side) {
         B200_CUDA(cudaEventRecord(ctx.ev_tail_done, ts));
-        ctx.tail_pending = true;
+        if (ctx.defer_tail) {
+            ctx.tail_pending = true;
+        } else {
+            B200_CUDA(cudaStreamWaitEvent(st, ctx.ev_tail_done, 0));
+        }
+    }
+    if (side) {  // overlapped: what is left after the last accumulation counts as carry rounds
+        B200_CUDA(cudaEventRecord(ctx.ev[PH_CARRY + 1], st));
+        B200_CUDA(cudaEventRecord(ctx.ev[PH_BUCKET_REDUCE + 1], st));
     }
     B200_CUDA(cudaEventRecord(ctx.ev[PH_FINAL + 1], st));
     return true;

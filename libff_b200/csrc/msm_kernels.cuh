@@ -232,12 +232,16 @@ template <class C>
 __global__ void __launch_bounds__(128)
     k_accum_first(const Entry *__restrict__ sorted, const uint32_t *__restrict__ offsets,
                   const uint32_t *__restrict__ seg_bucket, uint32_t total, uint32_t SEG,
-                  const uint32_t *__restrict__ aff, uint32_t *__restrict__ bucket_acc,
-                  uint32_t *__restrict__ carry_key, uint32_t *__restrict__ carry_pt) {
+                  uint32_t t_begin, uint32_t t_end, const uint32_t *__restrict__ aff,
+                  uint32_t *__restrict__ bucket_acc, uint32_t *__restrict__ carry_key,
+                  uint32_t *__restrict__ carry_pt) {
     using R = Raw<C>;
     using F = typename C::Fq;
     using X = XYZZ<F>;
-    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    // segments [t_begin, t_end): one group of windows (the host walks the windows top-down in
+    // groups so that the latency-bound reduction of one group runs under the next accumulation)
+    const uint32_t t = t_begin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= t_end) return;
     const uint64_t start64 = (uint64_t)t * SEG;
     if (start64 >= total) return;
     const uint32_t start = (uint32_t)start64;
@@ -288,31 +292,39 @@ __global__ void __launch_bounds__(128)
 
 // Later rounds: the carry list (keys ascending, one XYZZ point each) is reduced the same way with
 // full additions; sums of runs that begin a bucket in this list are added into bucket_acc.
+// The list is entries [begin, end) of keys / pts; only keys in [key_lo, key_hi) are live (a group
+// of windows shares its two boundary entries with its neighbours: each is live in exactly one).
+constexpr uint32_t CARRY_DEAD = 0xfffffffeu;
 template <class C>
 __global__ void __launch_bounds__(128)
     k_accum_carry(const uint32_t *__restrict__ keys, const uint32_t *__restrict__ pts,
-                  uint32_t total, uint32_t SEG, uint32_t *__restrict__ bucket_acc,
-                  uint32_t *__restrict__ carry_key, uint32_t *__restrict__ carry_pt) {
+                  uint32_t begin, uint32_t end, uint32_t key_lo, uint32_t key_hi, uint32_t SEG,
+                  uint32_t *__restrict__ bucket_acc, uint32_t *__restrict__ carry_key,
+                  uint32_t *__restrict__ carry_pt) {
     using R = Raw<C>;
     using F = typename C::Fq;
     using X = XYZZ<F>;
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    const uint64_t start64 = (uint64_t)t * SEG;
-    if (start64 >= total) return;
+    const uint64_t start64 = (uint64_t)begin + (uint64_t)t * SEG;
+    if (start64 >= end) return;
     const uint32_t start = (uint32_t)start64;
-    const uint32_t end = (uint32_t)min((uint64_t)total, start64 + SEG);
-    uint32_t cur = keys[start];
-    bool head_carry = start > 0 && keys[start - 1] == cur;
+    const uint32_t stop = (uint32_t)min((uint64_t)end, start64 + SEG);
+    auto key_at = [&](uint32_t pos) {
+        const uint32_t k = keys[pos];
+        return (k >= key_lo && k < key_hi) ? k : CARRY_DEAD;
+    };
+    uint32_t cur = key_at(start);
+    bool head_carry = cur != CARRY_DEAD && start > begin && key_at(start - 1) == cur;
     bool carried = false;
     carry_key[t] = cur;
     X acc = X::inf();
-    for (uint32_t pos = start; pos <= end; pos++) {
-        uint32_t k = pos < end ? keys[pos] : 0xffffffffu;
+    for (uint32_t pos = start; pos <= stop; pos++) {
+        uint32_t k = pos < stop ? key_at(pos) : 0xffffffffu;
         if (k != cur) {
             if (head_carry && !carried) {
                 acc.store(carry_pt + (size_t)t * R::XW);
                 carried = true;
-            } else if (!acc.is_inf()) {
+            } else if (cur != CARRY_DEAD && !acc.is_inf()) {
                 X b = X::load(bucket_acc + (size_t)cur * R::XW);
                 X::add(b, acc);
                 b.store(bucket_acc + (size_t)cur * R::XW);
@@ -321,7 +333,7 @@ __global__ void __launch_bounds__(128)
             cur = k;
             acc = X::inf();
         }
-        if (pos < end) {
+        if (pos < stop && k != CARRY_DEAD) {
             X q = X::load(pts + (size_t)pos * R::XW);
             X::add(acc, q);
         }
@@ -352,14 +364,14 @@ __device__ __noinline__ XYZZ<F> small_mul(const XYZZ<F> &p, uint32_t k) {
 template <class C>
 __global__ void __launch_bounds__(64)
     k_bucket_reduce(const uint32_t *__restrict__ bucket_acc, const uint32_t *__restrict__ hist,
-                    uint32_t B, uint32_t K, uint32_t *__restrict__ chunk_L,
+                    uint32_t B, uint32_t K, uint32_t w0, uint32_t *__restrict__ chunk_L,
                     uint32_t *__restrict__ chunk_T) {
     using R = Raw<C>;
     using F = typename C::Fq;
     using X = XYZZ<F>;
     const uint32_t chunks = B / K;
     const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
-    const uint32_t w = blockIdx.y;
+    const uint32_t w = w0 + blockIdx.y;
     if (j >= chunks) return;
     const uint32_t lo = j * K, hi = lo + K;
     X running = X::inf(), acc = X::inf();
@@ -383,13 +395,13 @@ __global__ void __launch_bounds__(64)
 template <class C, int THREADS>
 __global__ void __launch_bounds__(THREADS)
     k_window_reduce(const uint32_t *__restrict__ chunk_L, const uint32_t *__restrict__ chunk_T,
-                    uint32_t chunks, uint32_t log2K, uint32_t *__restrict__ window_sums,
-                    uint32_t *__restrict__ window_totals) {
+                    uint32_t chunks, uint32_t log2K, uint32_t w0,
+                    uint32_t *__restrict__ window_sums, uint32_t *__restrict__ window_totals) {
     using R = Raw<C>;
     using F = typename C::Fq;
     using X = XYZZ<F>;
     extern __shared__ uint32_t smem[];
-    const uint32_t w = blockIdx.x, t = threadIdx.x;
+    const uint32_t w = w0 + blockIdx.x, t = threadIdx.x;
     const uint32_t Q = chunks > (uint32_t)THREADS ? chunks / THREADS : 1u;
     const uint32_t log2Q = 31 - __clz(Q);
     X total = X::inf(), plain = X::inf();
@@ -473,9 +485,12 @@ __device__ __forceinline__ XYZZ<F> dbl_coop(const XYZZ<F> &p, uint32_t *sh, uint
 }
 
 // result = sum_w 2^(w c) window_sums[w] (Horner from the top window, multiexp.tcc:309-314),
-// written in the reference's coordinate system.  One warp; see dbl_coop.
+// written in the reference's coordinate system.  One warp; see dbl_coop.  The chain may be walked
+// in steps, one per group of windows [w_lo, w_hi) from the top group down: `state` carries the
+// running value between steps (read unless `first`), out_raw is written when `last`.
 template <class C>
-__global__ void __launch_bounds__(32) k_final(const uint32_t *__restrict__ window_sums, int W, int c,
+__global__ void __launch_bounds__(32) k_final(const uint32_t *__restrict__ window_sums, int w_lo, int w_hi,
+                                              int c, uint32_t *__restrict__ state, bool first, bool last,
                                               uint32_t *__restrict__ out_raw) {
     using R = Raw<C>;
     using F = typename C::Fq;
@@ -483,17 +498,20 @@ __global__ void __launch_bounds__(32) k_final(const uint32_t *__restrict__ windo
     __shared__ __align__(16) uint32_t sh[4 * F::N];
     if (blockIdx.x != 0) return;
     const uint32_t lane = threadIdx.x & 31;
-    X r = X::inf();
-    for (int w = W - 1; w >= 0; w--) {
+    X r = first ? X::inf() : X::load(state);
+    for (int w = w_hi - 1; w >= w_lo; w--) {
         if (!r.is_inf())  // uniform across the warp: every lane holds the same point
             for (int k = 0; k < c; k++) r = dbl_coop<F>(r, sh, lane);
         X q = X::load(window_sums + (size_t)w * R::XW);
         X::add(r, q);
     }
     if (lane == 0) {
-        F Xo, Yo, Zo;
-        R::from_xyzz(r, Xo, Yo, Zo);
-        R::store(out_raw, Xo, Yo, Zo);
+        if (!last) r.store(state);
+        if (last) {
+            F Xo, Yo, Zo;
+            R::from_xyzz(r, Xo, Yo, Zo);
+            R::store(out_raw, Xo, Yo, Zo);
+        }
     }
 }
 
