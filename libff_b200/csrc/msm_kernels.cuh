@@ -18,6 +18,7 @@
 // Any bucket-method schedule yields the same group element; parity is on the affine result.
 #pragma once
 #include "curves.cuh"
+#include "fp_coop.cuh"
 
 namespace b200msm {
 
@@ -484,6 +485,94 @@ __device__ __forceinline__ XYZZ<F> dbl_coop(const XYZZ<F> &p, uint32_t *sh, uint
     return XYZZ<F>{X3, Y3, ZZ3, F::load(sh + 2 * F::N)};
 }
 
+// The same doubling for the wide prime fields, every product spread over the lanes of a group
+// (fp_coop.cuh): groups 0..3 take the up to four products of a level.  `sh` has 4 * F::N words
+// for the results, `win` CoopField<F>::WIN_WORDS for the products' accumulator windows.
+template <class F>
+__device__ __forceinline__ XYZZ<F> dbl_coop_wide(const XYZZ<F> &p, uint32_t *sh, uint32_t *win,
+                                                 uint32_t lane) {
+    using CF = CoopField<F>;
+    const uint32_t g = (lane / CF::T) & 3u;            // product this lane works on
+    const bool writer = lane % CF::T == 0 && lane < 4 * CF::T;
+    const F U = F::dbl(p.Y);
+    // level 1: V = U^2, xx = X^2
+    F t = CF::mul(F::select(g == 1, p.X, U), F::select(g == 1, p.X, U), win, lane);
+    if (writer) t.store(sh + g * F::N);
+    __syncwarp();
+    const F V = F::load(sh), xx = F::load(sh + F::N);
+    __syncwarp();
+    const F M = F::add(F::dbl(xx), xx);
+    // level 2: W = U V, S = X V, M^2, ZZ' = V ZZ
+    t = CF::mul(g == 0 ? U : g == 1 ? p.X : g == 2 ? M : V, g == 0 ? V : g == 1 ? V : g == 2 ? M : p.ZZ,
+                win, lane);
+    if (writer) t.store(sh + g * F::N);
+    __syncwarp();
+    const F Wv = F::load(sh), S = F::load(sh + F::N), MM = F::load(sh + 2 * F::N),
+            ZZ3 = F::load(sh + 3 * F::N);
+    __syncwarp();
+    const F X3 = F::sub(MM, F::dbl(S));
+    // level 3: M (S - X3), W Y, ZZZ' = W ZZZ
+    t = CF::mul(g == 0 ? M : Wv, g == 0 ? F::sub(S, X3) : g == 1 ? p.Y : p.ZZZ, win, lane);
+    if (writer) t.store(sh + g * F::N);
+    __syncwarp();
+    const F Y3 = F::sub(F::load(sh), F::load(sh + F::N));
+    const F ZZZ3 = F::load(sh + 2 * F::N);
+    __syncwarp();
+    return XYZZ<F>{X3, Y3, ZZ3, ZZZ3};
+}
+
+// acc += q (add-2008-s, as XYZZ::add) with the 14 products in four levels of up to four
+// lane-parallel products.  Every lane holds both points; exceptional cases (an operand at
+// infinity, equal x) are uniform across the warp and take the one-lane routine.
+template <class F>
+__device__ __forceinline__ void add_coop_wide(XYZZ<F> &acc, const XYZZ<F> &q, uint32_t *sh,
+                                              uint32_t *win, uint32_t lane) {
+    using CF = CoopField<F>;
+    if (q.is_inf()) return;
+    if (acc.is_inf()) {
+        acc = q;
+        return;
+    }
+    const uint32_t g = (lane / CF::T) & 3u;
+    const bool writer = lane % CF::T == 0 && lane < 4 * CF::T;
+    // level 1: U1 = X1 ZZ2, S1 = Y1 ZZZ2, U2 = X2 ZZ1, S2 = Y2 ZZZ1
+    F t = CF::mul(g == 0 ? acc.X : g == 1 ? acc.Y : g == 2 ? q.X : q.Y,
+                  g == 0 ? q.ZZ : g == 1 ? q.ZZZ : g == 2 ? acc.ZZ : acc.ZZZ, win, lane);
+    if (writer) t.store(sh + g * F::N);
+    __syncwarp();
+    const F U1 = F::load(sh), S1 = F::load(sh + F::N);
+    const F Pd = F::sub(F::load(sh + 2 * F::N), U1), R = F::sub(F::load(sh + 3 * F::N), S1);
+    __syncwarp();
+    if (Pd.is_zero()) {  // uniform
+        XYZZ<F>::add(acc, q);
+        return;
+    }
+    // level 2: PP = P^2, RR = R^2, ZZ1 ZZ2, ZZZ1 ZZZ2
+    t = CF::mul(g == 0 ? Pd : g == 1 ? R : g == 2 ? acc.ZZ : acc.ZZZ,
+                g == 0 ? Pd : g == 1 ? R : g == 2 ? q.ZZ : q.ZZZ, win, lane);
+    if (writer) t.store(sh + g * F::N);
+    __syncwarp();
+    const F PP = F::load(sh), RR = F::load(sh + F::N), ZZ12 = F::load(sh + 2 * F::N),
+            ZZZ12 = F::load(sh + 3 * F::N);
+    __syncwarp();
+    // level 3: PPP = P PP, Q = U1 PP, ZZ3 = ZZ12 PP
+    t = CF::mul(g == 0 ? Pd : g == 1 ? U1 : ZZ12, PP, win, lane);
+    if (writer) t.store(sh + g * F::N);
+    __syncwarp();
+    const F PPP = F::load(sh), Q = F::load(sh + F::N), ZZ3 = F::load(sh + 2 * F::N);
+    __syncwarp();
+    const F X3 = F::sub(F::sub(RR, PPP), F::dbl(Q));
+    // level 4: R (Q - X3), S1 PPP, ZZZ3 = ZZZ12 PPP
+    t = CF::mul(g == 0 ? R : g == 1 ? S1 : ZZZ12, g == 0 ? F::sub(Q, X3) : PPP, win, lane);
+    if (writer) t.store(sh + g * F::N);
+    __syncwarp();
+    acc.X = X3;
+    acc.Y = F::sub(F::load(sh), F::load(sh + F::N));
+    acc.ZZ = ZZ3;
+    acc.ZZZ = F::load(sh + 2 * F::N);
+    __syncwarp();
+}
+
 // result = sum_w 2^(w c) window_sums[w] (Horner from the top window, multiexp.tcc:309-314),
 // written in the reference's coordinate system.  One warp; see dbl_coop.  The chain may be walked
 // in steps, one per group of windows [w_lo, w_hi) from the top group down: `state` carries the
@@ -496,14 +585,25 @@ __global__ void __launch_bounds__(32) k_final(const uint32_t *__restrict__ windo
     using F = typename C::Fq;
     using X = XYZZ<F>;
     __shared__ __align__(16) uint32_t sh[4 * F::N];
+    constexpr bool WIDE = CoopField<F>::OK;
+    __shared__ uint32_t win[CoopField<F>::WIN_WORDS];
     if (blockIdx.x != 0) return;
     const uint32_t lane = threadIdx.x & 31;
     X r = first ? X::inf() : X::load(state);
     for (int w = w_hi - 1; w >= w_lo; w--) {
-        if (!r.is_inf())  // uniform across the warp: every lane holds the same point
-            for (int k = 0; k < c; k++) r = dbl_coop<F>(r, sh, lane);
+        if (!r.is_inf()) {  // uniform across the warp: every lane holds the same point
+            for (int k = 0; k < c; k++) {
+                if constexpr (WIDE)
+                    r = dbl_coop_wide<F>(r, sh, win, lane);
+                else
+                    r = dbl_coop<F>(r, sh, lane);
+            }
+        }
         X q = X::load(window_sums + (size_t)w * R::XW);
-        X::add(r, q);
+        if constexpr (WIDE)
+            add_coop_wide<F>(r, q, sh, win, lane);
+        else
+            X::add(r, q);
     }
     if (lane == 0) {
         if (!last) r.store(state);
