@@ -28,8 +28,9 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-# the groups BASELINE.json's configs name (libff_b200/synthetic.py generates inputs for these)
-GROUP_IDS = {"alt_bn128_g1": 0, "alt_bn128_g2": 1, "bls12_377_g1": 2, "bw6_761_g1": 3}
+# the groups BASELINE.json's configs name come first; the default is alt_bn128_g1
+GROUP_IDS = {"alt_bn128_g1": 0, "alt_bn128_g2": 1, "bls12_377_g1": 2, "bw6_761_g1": 3,
+             "bls12_377_g2": 4, "bw6_761_g2": 5, "bls12_381_g1": 6, "bls12_381_g2": 7}
 # limb-MACs per point = W_ref * A * L with the reference's own window choice
 SCALAR_BITS = {0: 254, 1: 254, 2: 253, 3: 377, 4: 253, 5: 377, 6: 255, 7: 255}
 # Fq multiplications per mixed addition (Fq2: 7 M x 3 + 4 S x 2)
