@@ -163,14 +163,17 @@ size_t pick_parts(const Ctx &ctx, size_t n) {
     if (n < ((size_t)1 << 21)) return 1;
     if (n < ((size_t)1 << 22)) return 2;
     if (n < ((size_t)1 << 23)) return 3;
-    return 5;
+    // shared buckets: no per-range reduction, so more and shorter ranges pay (measured at 2^24:
+    // 12 ranges growing by 1.2x, profiles/e2e_sweep_r01e.log)
+    return ctx.opt_h2d_shared_buckets ? 12 : 5;
 }
 
 // Range boundaries of a pipelined call: sizes grow geometrically (x h2d_growth %, default 1.3),
 // so the first upload -- the only one nothing overlaps -- is short, while the later, longer MSMs
 // still finish after their successor's upload.  bounds has parts + 1 entries.
 void pick_bounds(const Ctx &ctx, size_t n, size_t parts, size_t *bounds) {
-    const double g = ctx.opt_h2d_growth > 0 ? ctx.opt_h2d_growth / 100.0 : 1.3;
+    const double g = ctx.opt_h2d_growth > 0 ? ctx.opt_h2d_growth / 100.0
+                     : (ctx.opt_h2d_shared_buckets && parts > 5) ? 1.2 : 1.3;
     double total = 0, w = 1;
     for (size_t k = 0; k < parts; k++, w *= g) total += w;
     double acc = 0;
@@ -379,8 +382,16 @@ bool b200msm_multi_exp(uint32_t group, const void *bases, size_t bases_bytes, co
     if (!ctx.reserve(SL_INF, n, &d_inf)) return false;
     if (!ctx.reserve(SL_SCALARS, scalars_bytes, &d_sc)) return false;
     if (!ctx.reserve(SL_OUT, ops->group_bytes, &d_out)) return false;
-    const size_t parts = pick_parts(ctx, n);
-    if (!ctx.reserve(SL_PARTIALS, parts * ops->group_bytes, &d_parts)) return false;
+    size_t parts = pick_parts(ctx, n);
+    size_t bounds[MAX_H2D_PARTS + 1] = {0};
+    if (parts > 1) {  // ranges that came out empty (tiny n) are dropped
+        pick_bounds(ctx, n, parts, bounds);
+        size_t m = 0;
+        for (size_t k = 0; k < parts; k++)
+            if (bounds[k + 1] > bounds[k]) bounds[++m] = bounds[k + 1];
+        parts = m;
+    }
+    if (!ctx.reserve(SL_PARTIALS, std::max<size_t>(parts, 1) * ops->group_bytes, &d_parts)) return false;
     B200_CUDA(cudaEventRecord(ctx.ev[0], ctx.stream));
     if (parts <= 1) {
         if (n > 0) {
@@ -394,8 +405,6 @@ bool b200msm_multi_exp(uint32_t group, const void *bases, size_t bases_bytes, co
     }
     // ---- pipelined: upload of range k + 1 (copy stream) under the MSM of range k
     const size_t gb = ops->group_bytes, sb = ops->scalar_bytes, ab = ops->affine_bytes;
-    size_t bounds[MAX_H2D_PARTS + 1];
-    pick_bounds(ctx, n, parts, bounds);
     auto lo_of = [&](size_t k) { return bounds[k]; };
     auto hi_of = [&](size_t k) { return bounds[k + 1]; };
     // the compute stream must not overwrite the staging buffers of a previous call that is
@@ -423,17 +432,27 @@ bool b200msm_multi_exp(uint32_t group, const void *bases, size_t bases_bytes, co
         }
     });
     if (!mark_all(ctx, PH_INGEST + 1)) return false;
-    // the latency-bound tail of range k runs under the kernels of range k + 1
+    // Shared buckets (default): every range is sorted and accumulated with the digit size of the
+    // whole call into ONE bucket set; the bucket reduction and the Horner chain run once, after
+    // the last range.  Otherwise (option h2d_shared_buckets = 0) every range is an independent
+    // MSM whose latency-bound tail runs under the kernels of range k + 1.
+    const bool shared = ctx.opt_h2d_shared_buckets != 0;
     struct TailScope {
         Ctx &c;
-        explicit TailScope(Ctx &c_) : c(c_) { c.defer_tail = true; }
+        TailScope(Ctx &c_, bool shared_, int range_c) : c(c_) {
+            c.defer_tail = !shared_;
+            c.range_c = shared_ ? range_c : 0;
+        }
         ~TailScope() {
             if (c.tail_pending) cudaStreamSynchronize(c.tail_stream);  // error paths
             c.defer_tail = c.tail_pending = false;
+            c.range_c = 0;
         }
-    } tail_scope(ctx);
+    } tail_scope(ctx, shared, (int)ops->window_bits(ctx, n));
     for (size_t k = 0; k < parts; k++) {
         const size_t lo = lo_of(k), cnt = hi_of(k) - lo;
+        ctx.range_first = k == 0;
+        ctx.range_last = k + 1 == parts;
         up.wait_for((int)k);
         if (up.failed) return set_error("multi_exp: host to device copy failed"), false;
         B200_CUDA(cudaStreamWaitEvent(ctx.stream, ctx.ev_copy[k], 0));
@@ -444,12 +463,27 @@ bool b200msm_multi_exp(uint32_t group, const void *bases, size_t bases_bytes, co
         if (!ops->msm(ctx, (char *)d_aff + lo * ab, (const uint8_t *)d_inf + lo, (char *)d_sc + lo * sb,
                       cnt, (char *)d_parts + k * gb, nullptr))
             return false;
+        if (ctx.opt_trace) {  // development aid: per-range phase times (serialises the pipeline)
+            B200_CUDA(cudaDeviceSynchronize());
+            fprintf(stderr, "[b200msm] range %zu: %zu points", k, cnt);
+            for (int p = PH_INGEST; p < PH_TOTAL; p++) {
+                float ms = 0;
+                B200_CUDA(cudaEventElapsedTime(&ms, ctx.ev[p], ctx.ev[p + 1]));
+                fprintf(stderr, " %s=%.3f", b200msm_timing_name((size_t)p), ms);
+            }
+            fprintf(stderr, "\n");
+        }
     }
     if (ctx.tail_pending) {
         B200_CUDA(cudaStreamWaitEvent(ctx.stream, ctx.ev_tail_done, 0));
         ctx.tail_pending = false;
     }
-    if (!ops->sum(ctx, d_parts, parts, d_out)) return false;
+    if (shared) {  // the last range reduced the shared buckets: its result is the result
+        B200_CUDA(cudaMemcpyAsync(d_out, (char *)d_parts + (parts - 1) * gb, gb,
+                                  cudaMemcpyDeviceToDevice, ctx.stream));
+    } else if (!ops->sum(ctx, d_parts, parts, d_out)) {
+        return false;
+    }
     return finish_msm(ctx, ops, d_out, out);
 }
 
@@ -956,6 +990,8 @@ bool b200msm_set_option(const char *name, int64_t value) {
         if (value < 0 || value > 400) return set_error("h2d_growth out of range (percent)"), false;
         return g_ctx->opt_h2d_growth = (int)value, true;
     }
+    if (name && !strcmp(name, "trace")) return g_ctx->opt_trace = value != 0, true;
+    if (name && !strcmp(name, "h2d_shared_buckets")) return g_ctx->opt_h2d_shared_buckets = value != 0, true;
     if (name && !strcmp(name, "h2d_parts")) {
         if (value < 0 || value > MAX_H2D_PARTS) return set_error("h2d_parts out of range"), false;
         return g_ctx->opt_h2d_parts = (int)value, true;

@@ -76,6 +76,7 @@ enum Slot {
     SL_PRE_STATE,   // XYZZ running multiples while a table is built
     SL_PRE_RAW,     // the same in reference layout, input of the batch normalisation
     SL_STREAM_IN,   // encoded chunk of a streamed MSM
+    SL_LIVE,        // per bucket: written by an earlier point range of the same call
     SL_COUNT
 };
 
@@ -97,6 +98,11 @@ struct Ctx {
     cudaStream_t acc_stream = nullptr;
     cudaEvent_t ev_group_go = nullptr, ev_group[2] = {};
     bool defer_tail = false;    // set by the pipelined caller
+    // Point ranges of ONE host-buffer call that share a bucket set (set by the pipelined caller):
+    // every range runs digits / sort / accumulation with the digit size of the whole call and adds
+    // into the same buckets; only the last range reduces the buckets.  range_c == 0: off.
+    int range_c = 0;
+    bool range_first = false, range_last = false;
     bool tail_pending = false;  // a deferred tail may still be reading the reduction scratch
     void *slot_ptr[SL_COUNT] = {};
     size_t slot_bytes[SL_COUNT] = {};
@@ -108,6 +114,8 @@ struct Ctx {
     int opt_window_bits = 0;  // 0 = automatic
     int opt_segment = 0;      // 0 = default
     int opt_h2d_parts = 0;    // 0 = automatic
+    int opt_h2d_shared_buckets = 1; // upload ranges of one call share a bucket set (else: one MSM each)
+    int opt_trace = 0;        // print per-range phase times of a pipelined call (development aid)
     int opt_h2d_growth = 0;   // size ratio of consecutive ranges in percent; 0 = default (130)
     int opt_window_groups = 0; // groups the windows are walked in (top-down); 0 = automatic, 1 = one
     int opt_carry_segment = 0; // carries per thread in the later accumulation rounds; 0 = automatic

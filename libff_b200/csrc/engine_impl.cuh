@@ -165,7 +165,10 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
         return false;
     }
     const bool pre = shape != nullptr;
-    const int c = pre ? shape->c : (int)pick_window_bits<C>(ctx, n);
+    // shared-bucket point ranges of one call (Ctx::range_c): fixed digit size, buckets kept
+    const bool ranged = !pre && ctx.range_c > 0;
+    const bool range_first = !ranged || ctx.range_first, range_last = !ranged || ctx.range_last;
+    const int c = pre ? shape->c : ranged ? ctx.range_c : (int)pick_window_bits<C>(ctx, n);
     const int W = pre ? shape->W : (C::Fr::Params::BITS + 1 + c - 1) / c;
     const uint32_t B = 1u << (c - 1);
     const uint32_t bstride = pre ? 0u : B;         // precomputed multiples share one bucket set
@@ -187,7 +190,13 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
 
     // --- digits + histogram
     B200_CUDA(cudaMemsetAsync(hist, 0, M * 4, st));
-    B200_CUDA(cudaMemsetAsync(offsets + M + 1, 0, 4, st));
+    // (the highest used window is a maximum over all ranges of a call)
+    if (range_first) B200_CUDA(cudaMemsetAsync(offsets + M + 1, 0, 4, st));
+    uint32_t *live = nullptr;
+    if (ranged) {
+        if (!reserve_as(ctx, SL_LIVE, M * 4, &live)) return false;
+        if (range_first) B200_CUDA(cudaMemsetAsync(live, 0, M * 4, st));
+    }
     uint32_t *ranks;
     if (!reserve_as(ctx, SL_RANKS, (size_t)W * n * 4, &ranks)) return false;
     k_digits<C><<<cdiv(n, 256), 256, 0, st>>>((const uint32_t *)d_scalars, d_inf, digits, ranks, hist,
@@ -216,6 +225,7 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
     B200_CUDA(cudaStreamSynchronize(st));
     const uint32_t total = meta[0];
     // windows (bucket sets) that hold items
+    // (an earlier range may have used higher windows than this one: meta[1] is cumulative)
     const int Wu = pre ? 1 : std::max<int>(1, std::min<int>(W, (int)meta[1]));
     const uint32_t seg = pick_segment(ctx, total);
     const size_t t1 = ((size_t)total + seg - 1) / seg;
@@ -274,7 +284,7 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
         int lo, hi;  // windows [lo, hi)
     };
     std::vector<Group> groups;  // top-down
-    if (pre || total == 0) {
+    if (pre || total == 0 || ranged) {
         groups.push_back(Group{0, Wr});
     } else {
         int ng = ctx.opt_window_groups;
@@ -310,7 +320,9 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
         }
     }
     const size_t G = groups.size();
-    const bool side = G > 1 || ctx.defer_tail;      // tails on the side stream
+    // tails on the side stream; for a range that is not the last one the "tail" is its carry
+    // rounds, which run under the digit pass and the sort of the next range
+    const bool side = G > 1 || ctx.defer_tail || (ranged && !range_last);
     cudaStream_t ts = side ? ctx.tail_stream : st;
     const uint32_t SEG_CARRY = pick_carry_segment<C>(ctx);
     uint32_t *keyA = nullptr, *ptA = nullptr, *keyB = nullptr, *ptB = nullptr, *keyC = nullptr, *ptC = nullptr;
@@ -338,9 +350,14 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
             const uint32_t tb = (pre || last) ? 0u : seg_of_window(gr.lo);
             const uint32_t te = (pre || first) ? (uint32_t)t1 : seg_of_window(gr.hi);
             if (te > tb) {
-                k_accum_first<C><<<cdiv(te - tb, 128), 128, 0, as>>>(
-                    sorted, offsets, seg_bucket, total, seg, tb, te, (const uint32_t *)d_aff, buckets,
-                    keyA, ptA);
+                if (ranged)
+                    k_accum_first_merge<C><<<cdiv(te - tb, 128), 128, 0, as>>>(
+                        sorted, offsets, seg_bucket, total, seg, tb, te, (const uint32_t *)d_aff,
+                        buckets, keyA, ptA, live);
+                else
+                    k_accum_first<C><<<cdiv(te - tb, 128), 128, 0, as>>>(
+                        sorted, offsets, seg_bucket, total, seg, tb, te, (const uint32_t *)d_aff,
+                        buckets, keyA, ptA);
                 B200_LAUNCH_CHECK(ctx);
             }
             if (side) {
@@ -370,9 +387,10 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
             B200_CUDA(cudaEventRecord(ctx.ev[PH_ACCUM + 1], st));
         }
         if (!side) B200_CUDA(cudaEventRecord(ctx.ev[PH_CARRY + 1], st));
+        if (!range_last) break;  // the buckets stay; the next range of the call adds to them
         // bucket reduction, window totals, Horner stretch of this group
         k_bucket_reduce<C><<<dim3(cdiv(nchunks, 64), gr.hi - gr.lo), 64, 0, ts>>>(
-            buckets, hist, Br, K, (uint32_t)gr.lo, chunks, chunk_T);
+            buckets, ranged ? live : hist, Br, K, (uint32_t)gr.lo, chunks, chunk_T);
         B200_LAUNCH_CHECK(ctx);
         if (!side) B200_CUDA(cudaEventRecord(ctx.ev[PH_BUCKET_REDUCE + 1], st));
         if (last && ctx.defer_tail) {
@@ -396,7 +414,7 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
     }
     if (side) {
         B200_CUDA(cudaEventRecord(ctx.ev_tail_done, ts));
-        if (ctx.defer_tail) {
+        if (ctx.defer_tail || (ranged && !range_last)) {
             ctx.tail_pending = true;
         } else {
             B200_CUDA(cudaStreamWaitEvent(st, ctx.ev_tail_done, 0));

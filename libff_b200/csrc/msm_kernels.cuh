@@ -229,13 +229,16 @@ __global__ void k_scatter(const int32_t *__restrict__ digits, const uint32_t *__
 // First accumulation round: thread t owns sorted[t*SEG, (t+1)*SEG) (SEG chosen by the host, a
 // multiple of 4).  Bucket boundaries come from the offsets array, walked from the segment's
 // first bucket (recorded by the scatter).
-template <class C>
-__global__ void __launch_bounds__(128)
-    k_accum_first(const Entry *__restrict__ sorted, const uint32_t *__restrict__ offsets,
-                  const uint32_t *__restrict__ seg_bucket, uint32_t total, uint32_t SEG,
-                  uint32_t t_begin, uint32_t t_end, const uint32_t *__restrict__ aff,
-                  uint32_t *__restrict__ bucket_acc, uint32_t *__restrict__ carry_key,
-                  uint32_t *__restrict__ carry_pt) {
+// MERGE: the buckets already hold the sums of earlier point ranges of the same call (one bucket
+// set shared by all upload ranges of a host-buffer multi_exp).  `live[b] != 0` says bucket b has
+// been written before; the thread that owns the head of a run starts from that value instead of
+// the neutral element and marks the bucket live.  Exactly one thread per launch owns a bucket.
+template <class C, bool MERGE>
+__device__ __forceinline__ void accum_first_body(
+    const Entry *__restrict__ sorted, const uint32_t *__restrict__ offsets,
+    const uint32_t *__restrict__ seg_bucket, uint32_t total, uint32_t SEG, uint32_t t_begin,
+    uint32_t t_end, const uint32_t *__restrict__ aff, uint32_t *__restrict__ bucket_acc,
+    uint32_t *__restrict__ carry_key, uint32_t *__restrict__ carry_pt, uint32_t *live) {
     using R = Raw<C>;
     using F = typename C::Fq;
     using X = XYZZ<F>;
@@ -254,6 +257,10 @@ __global__ void __launch_bounds__(128)
     carry_key[t] = cur;
     bool carried = false;
     X acc = X::inf();
+    if (MERGE && !head_carry) {
+        if (live[cur] != 0) acc = X::load(bucket_acc + (size_t)cur * R::XW);
+        live[cur] = 1;
+    }
     uint4 q = *reinterpret_cast<const uint4 *>(sorted + start);  // 4 items per load
     Entry e = q.x;
     Affine<F> p = Affine<F>::load(aff + (size_t)(e & 0x7fffffffu) * R::AW);
@@ -279,6 +286,10 @@ __global__ void __launch_bounds__(128)
                 next = offsets[cur + 1];
             } while (next <= pos);  // skip empty buckets
             acc = X::inf();
+            if (MERGE) {
+                if (live[cur] != 0) acc = X::load(bucket_acc + (size_t)cur * R::XW);
+                live[cur] = 1;
+            }
         }
         X::madd(acc, pcur.x, F::cneg(pcur.y, (ecur >> 31) != 0));
     }
@@ -289,6 +300,28 @@ __global__ void __launch_bounds__(128)
         acc.store(bucket_acc + (size_t)cur * R::XW);
     }
     if (!carried) X::inf().store(carry_pt + (size_t)t * R::XW);
+}
+
+template <class C>
+__global__ void __launch_bounds__(128)
+    k_accum_first(const Entry *__restrict__ sorted, const uint32_t *__restrict__ offsets,
+                  const uint32_t *__restrict__ seg_bucket, uint32_t total, uint32_t SEG,
+                  uint32_t t_begin, uint32_t t_end, const uint32_t *__restrict__ aff,
+                  uint32_t *__restrict__ bucket_acc, uint32_t *__restrict__ carry_key,
+                  uint32_t *__restrict__ carry_pt) {
+    accum_first_body<C, false>(sorted, offsets, seg_bucket, total, SEG, t_begin, t_end, aff,
+                               bucket_acc, carry_key, carry_pt, nullptr);
+}
+
+template <class C>
+__global__ void __launch_bounds__(128)
+    k_accum_first_merge(const Entry *__restrict__ sorted, const uint32_t *__restrict__ offsets,
+                        const uint32_t *__restrict__ seg_bucket, uint32_t total, uint32_t SEG,
+                        uint32_t t_begin, uint32_t t_end, const uint32_t *__restrict__ aff,
+                        uint32_t *__restrict__ bucket_acc, uint32_t *__restrict__ carry_key,
+                        uint32_t *__restrict__ carry_pt, uint32_t *__restrict__ live) {
+    accum_first_body<C, true>(sorted, offsets, seg_bucket, total, SEG, t_begin, t_end, aff,
+                              bucket_acc, carry_key, carry_pt, live);
 }
 
 // Later rounds: the carry list (keys ascending, one XYZZ point each) is reduced the same way with

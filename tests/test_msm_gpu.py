@@ -254,16 +254,20 @@ def test_multi_exp_segment_lengths(engine, ref, seg):
 
 
 @pytest.mark.parametrize("gid", GROUPS)
+@pytest.mark.parametrize("shared", [1, 0])
 @pytest.mark.parametrize("parts", [1, 2, 3, 7])
-def test_multi_exp_pipelined_upload(engine, ref, gid, parts):
-    """Host-buffer calls cut the point range into `h2d_parts` independently uploaded and computed
-    ranges (upload of range k + 1 under the MSM of range k); the sum of the partial results is the
-    same element (multiexp.tcc:663-687 does the same split across threads)."""
+def test_multi_exp_pipelined_upload(engine, ref, gid, parts, shared):
+    """Host-buffer calls cut the point range into `h2d_parts` independently uploaded ranges (upload
+    of range k + 1 under the kernels of range k).  shared = 1 (default): all ranges are sorted with
+    the digit size of the whole call and accumulate into ONE bucket set that is reduced once;
+    shared = 0: every range is an MSM of its own and the partial results are added
+    (multiexp.tcc:663-687 does the same split across threads).  Same element either way."""
     n = {0: 1003, 1: 301, 2: 502, 3: 99, 4: 99, 5: 99, 6: 502, 7: 99}[gid]
     aff = ref.gen_bases_walk(gid, n + 1)
     jac = ref.group_op(gid, ref.G_ADD, aff[:-1], aff[1:])
     scalars = ref.gen_scalars(gid, n, start=21)
     engine.set_option("h2d_parts", parts)
+    engine.set_option("h2d_shared_buckets", shared)
     try:
         assert_same_point(ref, gid, engine.multi_exp(gid, aff[:n], scalars), ref.multi_exp(gid, aff[:n], scalars))
         assert_same_point(ref, gid, engine.multi_exp(gid, jac, scalars, base_form=engine.FORM_NORMAL),
@@ -271,6 +275,46 @@ def test_multi_exp_pipelined_upload(engine, ref, gid, parts):
         assert_same_point(ref, gid, engine.multi_exp(gid, aff[:2], scalars[:2]), ref.multi_exp(gid, aff[:2], scalars[:2]))
     finally:
         engine.set_option("h2d_parts", 0)
+        engine.set_option("h2d_shared_buckets", 1)
+
+
+@pytest.mark.parametrize("gid", GROUPS)
+@pytest.mark.parametrize("window_bits", [0, 3, 9])
+def test_multi_exp_shared_bucket_ranges_edge_cases(engine, ref, gid, window_bits):
+    """The shared bucket set across upload ranges: buckets that an earlier range filled and a later
+    one extends, ranges whose scalars are all zero (no items at all, first / middle / last range),
+    a later range that only uses low windows after an earlier one used all of them, repeated
+    bases and P + (-P) meeting in one bucket across two ranges, infinity among the bases."""
+    g = pm.GROUPS[gid]
+    n = {0: 600, 1: 240, 2: 360, 3: 96, 4: 96, 5: 96, 6: 360, 7: 96}[gid]
+    parts = 4
+    q = n // parts
+    bases = ref.gen_bases_walk(gid, n)
+    full = g.decode_scalars(ref.gen_scalars(gid, n, start=77))
+    r = g.fr.p
+    zero, _ = ref.group_constants(gid)
+    cases = []
+    for zero_part in (0, 2, 3):            # one range contributes nothing
+        cases.append((bases, [0 if i // q == zero_part else v for i, v in enumerate(full)]))
+    # high windows only in the first range, tiny scalars afterwards
+    cases.append((bases, [v if i < q else (v % 7) for i, v in enumerate(full)]))
+    # the same base with the same digit in every range; then cancelling pairs across ranges
+    same = np.repeat(bases[:1], n, axis=0)
+    cases.append((same, [5] * n))
+    cases.append((same, [(5 if (i // q) % 2 == 0 else r - 5) for i in range(n)]))
+    # infinity bases (encoded as the reference does) in every range
+    with_inf = bases.copy()
+    with_inf[::q] = zero
+    cases.append((with_inf, full))
+    engine.set_option("h2d_parts", parts)
+    engine.set_option("window_bits", window_bits)
+    try:
+        for b, vals in cases:
+            sc = g.encode_scalars(vals)
+            assert_same_point(ref, gid, engine.multi_exp(gid, b, sc), ref.multi_exp(gid, b, sc))
+    finally:
+        engine.set_option("h2d_parts", 0)
+        engine.set_option("window_bits", 0)
 
 
 @pytest.mark.parametrize("gid", GROUPS)

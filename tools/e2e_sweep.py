@@ -30,7 +30,9 @@ want = m.batch_to_special(gid, want.reshape(1, -1))[0]
 hb = torch.from_numpy(bases).pin_memory()
 hs = torch.from_numpy(scalars).pin_memory()
 growths = [int(x) for x in os.environ.get("GROWTH", "0").split(",")]
-for p, gr in [(p, gr) for p in parts for gr in growths]:
+shareds = [int(x) for x in os.environ.get("SHARED", "1").split(",")]
+for sh, p, gr in [(sh, p, gr) for sh in shareds for p in parts for gr in growths]:
+    m.set_option("h2d_shared_buckets", sh)
     m.set_option("h2d_parts", p)
     m.set_option("h2d_growth", gr)
     best = 1e9
@@ -39,4 +41,4 @@ for p, gr in [(p, gr) for p in parts for gr in growths]:
         got = m.multi_exp_host_ptr(gid, hb.data_ptr(), hs.data_ptr(), n)
         best = min(best, m.timer_stop())
     ok = bool(np.array_equal(m.batch_to_special(gid, got.reshape(1, -1))[0], want))
-    print(f"h2d_parts={p} growth={gr}: e2e {best:.2f} ms = {n / best / 1e3:.1f} M points/s  same={ok}", flush=True)
+    print(f"shared={sh} h2d_parts={p} growth={gr}: e2e {best:.2f} ms = {n / best / 1e3:.1f} M points/s  same={ok}", flush=True)
