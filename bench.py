@@ -43,7 +43,26 @@ MIN_BYTES = {0: 96, 1: 160, 2: 128, 3: 240, 4: 224, 5: 240, 6: 128, 7: 224}
 
 # ncu --set full, k_accum_first, per launch: 28.72 GB read + 1.28 GB written
 # (profiles/accum_first_r01d_raw.csv)
-NCU_TRAFFIC = {("alt_bn128_g1", 1 << 24): 30.00e9}
+NCU_TRAFFIC = {("alt_bn128_g1", 1 << 24): 30.00e9, ("bls12_377_g1", 1 << 22): 11.31e9,
+               ("alt_bn128_g2", 1 << 20): 2.68e9, ("bw6_761_g1", 1 << 19): 6.18e9}
+# sm__pipe_fmaheavy_cycles_active (the pipe IMAD / IMAD.WIDE issue on) of k_accum_first in the
+# committed `ncu --set full` captures: the hardware-side utilisation figure next to `frac`
+NCU_PIPE_UTIL = {("alt_bn128_g1", 1 << 24): (0.897, "profiles/accum_first_r01d_raw.csv"),
+                 ("bls12_377_g1", 1 << 22): (0.749, "profiles/accum_first_bls12_377_g1_r01e_raw.csv"),
+                 ("alt_bn128_g2", 1 << 20): (0.670, "profiles/accum_first_alt_bn128_g2_r01e_raw.csv"),
+                 ("bw6_761_g1", 1 << 19): (0.641, "profiles/accum_first_bw6_761_g1_r01e_raw.csv")}
+
+
+def executed_macs_per_item(gid):
+    """Limb products this engine issues per accumulated item (one XYZZ mixed addition, 8M + 2S):
+    six plain products (2N^2 + N), one two-product sum with a shared reduction (3N^2 + 2N) and two
+    dedicated squarings (N(N+1)/2 + N^2 + N); over Fp2 a product is three and a squaring two
+    base-field products (Karatsuba / complex squaring)."""
+    N = {136: 8, 300: 12, 1176: 24}[MUL_MACS[gid]]
+    mul, sqr, mul2 = 2 * N * N + N, N * (N + 1) // 2 + N * N + N, 3 * N * N + 2 * N
+    if ADD_COST[gid] == 11:
+        return 6 * mul + mul2 + 2 * sqr
+    return (8 * 3 + 2 * 2) * mul
 
 
 def ceil_log2(n):
@@ -288,6 +307,8 @@ def main():
 
     # ---- roofline of the dominant kernel (bucket accumulation), integer-multiply pipe
     peak, micro = measure_int_peak()
+    c_eng = m.window_bits(gid, n)
+    engine_windows = -(-(SCALAR_BITS[gid] + 1) // c_eng)
     achieved = n * macs * 2 / (accum_ms * 1e-3) / 1e12  # T IMAD slots/s, SURVEY.md §8d convention
     peaks_file = os.path.join(ROOT, "MEASURED_PEAKS.json")
     hbm_peak = json.load(open(peaks_file))["hbm_gbs"] if os.path.exists(peaks_file) else 6650.0
@@ -299,6 +320,14 @@ def main():
         "algorithmic_unit": f"{macs} limb-MACs/point (W_ref={w_ref} x A={ADD_COST[gid]} x "
                             f"L={MUL_MACS[gid]}, c_ref={c_ref}) x 2 IMAD slots",
         "kernel_ms": accum_ms, "kernel_share_of_step": accum_ms / phase_ms["total"],
+        # the limb products the kernel really issues (signed digits, this run's digit size, XYZZ
+        # mixed additions with dedicated squarings) against the same peak: always <= 1
+        "executed": {"frac": n * engine_windows * executed_macs_per_item(gid) * 2
+                     / (accum_ms * 1e-3) / 1e12 / peak,
+                     "unit": f"n x {engine_windows} digits x {executed_macs_per_item(gid)} "
+                             "limb products x 2 IMAD slots / kernel time / peak"},
+        "pipe_utilisation_ncu": dict(zip(("fmaheavy_cycles_active", "source"),
+                                         NCU_PIPE_UTIL.get((args.group, n), (None, None)))),
         # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the committed
         # `ncu --set full` capture of this workload (profiles/accum_first_r01d_raw.csv)
         "traffic": NCU_TRAFFIC.get((args.group, n)),

@@ -67,7 +67,8 @@ _bound_device: Optional[int] = None
 
 
 def lib_path() -> str:
-    return os.path.join(_HERE, "libb200msm.so")
+    # B200MSM_LIB: development aid for A/B runs of differently compiled engines
+    return os.environ.get("B200MSM_LIB") or os.path.join(_HERE, "libb200msm.so")
 
 
 def load():

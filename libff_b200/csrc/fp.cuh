@@ -27,6 +27,11 @@
 namespace b200msm {
 
 #define B200_DEV __device__ __forceinline__
+// Fields of at least this many 32-bit limbs call one shared copy of the Montgomery product
+// instead of inlining it at every use (instruction-cache footprint against call overhead).
+#ifndef B200_CALL_MIN_LIMBS
+#define B200_CALL_MIN_LIMBS 24
+#endif
 
 namespace limb {
 
@@ -107,7 +112,10 @@ B200_DEV void row_acc_shift_from(uint32_t *acc, const uint32_t *a, uint32_t bi) 
 
 }  // namespace limb
 
-template <class P>
+// CALL_MIN: fields of at least this many limbs call one shared copy of the product (see
+// B200_CALL_MIN_LIMBS); kernels pick the policy per use through Rebind (fp2.cuh): the layout of
+// an element does not depend on it.
+template <class P, int CALL_MIN = B200_CALL_MIN_LIMBS>
 struct Fp {
     static constexpr int N = P::N;
     using Params = P;
@@ -312,7 +320,7 @@ struct Fp {
     // product (a 24-limb product is ~1300 instructions; inlining a dozen per group operation
     // only thrashes the instruction cache and the compiler).
     B200_DEV static Fp mul(const Fp &a, const Fp &b) {
-        if constexpr (N >= 24)
+        if constexpr (N >= CALL_MIN)
             return mul_call(a, b);
         else
             return mul_inline(a, b);
@@ -332,7 +340,7 @@ struct Fp {
     B200_DEV static Fp sqr(const Fp &a) {
         if constexpr (!SPARE2)
             return mul(a, a);
-        else if constexpr (N >= 24)
+        else if constexpr (N >= CALL_MIN)
             return sqr_call(a);
         else
             return sqr_inline(a);
@@ -354,7 +362,7 @@ struct Fp {
     B200_DEV static Fp mul2(const Fp &a, const Fp &b, const Fp &c, const Fp &d) {
         if constexpr (!SPARE2)
             return add(mul(a, b), mul(c, d));
-        else if constexpr (N >= 24)
+        else if constexpr (N >= CALL_MIN)
             return mul2_call(a, b, c, d);
         else
             return mul2_inline(a, b, c, d);

@@ -12,9 +12,9 @@
 
 namespace b200msm {
 
-template <class P, int NR = 1>
+template <class P, int NR = 1, int CALL_MIN = B200_CALL_MIN_LIMBS>
 struct Fp2 {
-    using F = Fp<P>;
+    using F = Fp<P, CALL_MIN>;
     static constexpr int N = 2 * P::N;  // 32-bit words per element
     using Params = P;
     F c0, c1;
@@ -80,5 +80,46 @@ struct Fp2 {
         c1.store(p + P::N);
     }
 };
+
+// The same field with another inline / call policy for its base-field products (CALL_MIN limbs).
+template <class F, int CM>
+struct Rebind;
+template <class P, int X, int CM>
+struct Rebind<Fp<P, X>, CM> {
+    using type = Fp<P, CM>;
+};
+template <class P, int NR, int X, int CM>
+struct Rebind<Fp2<P, NR, X>, CM> {
+    using type = Fp2<P, NR, CM>;
+};
+template <class F>
+struct BaseLimbs;
+template <class P, int X>
+struct BaseLimbs<Fp<P, X>> {
+    static constexpr int N = P::N;
+    static constexpr bool EXT = false;
+};
+template <class P, int NR, int X>
+struct BaseLimbs<Fp2<P, NR, X>> {
+    static constexpr int N = P::N;
+    static constexpr bool EXT = true;
+};
+// Tail kernels (carry rounds, bucket reduction, window totals) are latency- and instruction-cache
+// bound: with 12-limb products inlined they are 270 KB of code; calling one shared copy is
+// faster there (bls12_377 G1 2^22: carry rounds 2.65 -> 1.82 ms, bucket reduction 2.35 -> 1.73).
+#ifndef B200_TAIL_CALL_MIN_LIMBS
+#define B200_TAIL_CALL_MIN_LIMBS 12
+#endif
+template <class F>
+using TailField = typename Rebind<F, (BaseLimbs<F>::N >= B200_CALL_MIN_LIMBS         ? B200_CALL_MIN_LIMBS
+                                      : BaseLimbs<F>::N >= B200_TAIL_CALL_MIN_LIMBS ? B200_TAIL_CALL_MIN_LIMBS
+                                                                                    : B200_CALL_MIN_LIMBS)>::type;
+// The accumulation kernel inlines the products of 12-limb prime fields (calls cost 28.5 -> 37.8 ms
+// there) but calls them for the 12-limb quadratic extensions (38.3 -> 33.6 ms: three base-field
+// products per product no longer fit the instruction cache).
+template <class F>
+using AccumField = typename Rebind<F, (BaseLimbs<F>::EXT && BaseLimbs<F>::N >= 12
+                                           ? 12
+                                           : B200_CALL_MIN_LIMBS)>::type;
 
 }  // namespace b200msm

@@ -24,9 +24,9 @@ struct CoopField {
     static constexpr int WIN_WORDS = 1;
 };
 
-template <class P>
-struct CoopField<Fp<P>> {
-    using F = Fp<P>;
+template <class P, int CM>
+struct CoopField<Fp<P, CM>> {
+    using F = Fp<P, CM>;
     static constexpr int N = P::N;
     static constexpr bool OK = N >= 12 && N % 4 == 0 && F::SPARE2;
     static constexpr int T = (N % 8 == 0 && N >= 16) ? 8 : 4;  // lanes per product

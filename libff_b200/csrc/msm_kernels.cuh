@@ -233,6 +233,15 @@ __global__ void k_scatter(const int32_t *__restrict__ digits, const uint32_t *__
 // set shared by all upload ranges of a host-buffer multi_exp).  `live[b] != 0` says bucket b has
 // been written before; the thread that owns the head of a run starts from that value instead of
 // the neutral element and marks the bucket live.  Exactly one thread per launch owns a bucket.
+// L2 prefetch of one bucket accumulator (XW words; a prefetch never faults, so running past the
+// last bucket is harmless)
+template <int XW>
+__device__ __forceinline__ void prefetch_bucket(const uint32_t *bucket_acc, uint32_t b) {
+    const char *p = reinterpret_cast<const char *>(bucket_acc + (size_t)b * XW);
+#pragma unroll
+    for (int o = 0; o < XW * 4; o += 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + o));
+}
+
 template <class C, bool MERGE>
 __device__ __forceinline__ void accum_first_body(
     const Entry *__restrict__ sorted, const uint32_t *__restrict__ offsets,
@@ -240,7 +249,7 @@ __device__ __forceinline__ void accum_first_body(
     uint32_t t_end, const uint32_t *__restrict__ aff, uint32_t *__restrict__ bucket_acc,
     uint32_t *__restrict__ carry_key, uint32_t *__restrict__ carry_pt, uint32_t *live) {
     using R = Raw<C>;
-    using F = typename C::Fq;
+    using F = AccumField<typename C::Fq>;
     using X = XYZZ<F>;
     // segments [t_begin, t_end): one group of windows (the host walks the windows top-down in
     // groups so that the latency-bound reduction of one group runs under the next accumulation)
@@ -257,9 +266,14 @@ __device__ __forceinline__ void accum_first_body(
     carry_key[t] = cur;
     bool carried = false;
     X acc = X::inf();
-    if (MERGE && !head_carry) {
-        if (live[cur] != 0) acc = X::load(bucket_acc + (size_t)cur * R::XW);
-        live[cur] = 1;
+    if (MERGE) {
+        // the thread walks consecutive buckets: pull the next accumulators towards the SM early
+        prefetch_bucket<R::XW>(bucket_acc, cur + 1);
+        prefetch_bucket<R::XW>(bucket_acc, cur + 2);
+        if (!head_carry) {
+            if (live[cur] != 0) acc = X::load(bucket_acc + (size_t)cur * R::XW);
+            live[cur] = 1;
+        }
     }
     uint4 q = *reinterpret_cast<const uint4 *>(sorted + start);  // 4 items per load
     Entry e = q.x;
@@ -287,6 +301,7 @@ __device__ __forceinline__ void accum_first_body(
             } while (next <= pos);  // skip empty buckets
             acc = X::inf();
             if (MERGE) {
+                prefetch_bucket<R::XW>(bucket_acc, cur + 2);
                 if (live[cur] != 0) acc = X::load(bucket_acc + (size_t)cur * R::XW);
                 live[cur] = 1;
             }
@@ -314,7 +329,7 @@ __global__ void __launch_bounds__(128)
 }
 
 template <class C>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, Raw<C>::XW <= 32 ? 4 : 1)
     k_accum_first_merge(const Entry *__restrict__ sorted, const uint32_t *__restrict__ offsets,
                         const uint32_t *__restrict__ seg_bucket, uint32_t total, uint32_t SEG,
                         uint32_t t_begin, uint32_t t_end, const uint32_t *__restrict__ aff,
@@ -336,7 +351,7 @@ __global__ void __launch_bounds__(128)
                   uint32_t *__restrict__ bucket_acc, uint32_t *__restrict__ carry_key,
                   uint32_t *__restrict__ carry_pt) {
     using R = Raw<C>;
-    using F = typename C::Fq;
+    using F = TailField<typename C::Fq>;
     using X = XYZZ<F>;
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     const uint64_t start64 = (uint64_t)begin + (uint64_t)t * SEG;
@@ -401,7 +416,7 @@ __global__ void __launch_bounds__(64)
                     uint32_t B, uint32_t K, uint32_t w0, uint32_t *__restrict__ chunk_L,
                     uint32_t *__restrict__ chunk_T) {
     using R = Raw<C>;
-    using F = typename C::Fq;
+    using F = TailField<typename C::Fq>;
     using X = XYZZ<F>;
     const uint32_t chunks = B / K;
     const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
@@ -432,7 +447,7 @@ __global__ void __launch_bounds__(THREADS)
                     uint32_t chunks, uint32_t log2K, uint32_t w0,
                     uint32_t *__restrict__ window_sums, uint32_t *__restrict__ window_totals) {
     using R = Raw<C>;
-    using F = typename C::Fq;
+    using F = TailField<typename C::Fq>;
     using X = XYZZ<F>;
     extern __shared__ uint32_t smem[];
     const uint32_t w = w0 + blockIdx.x, t = threadIdx.x;
