@@ -504,8 +504,100 @@ __global__ void __launch_bounds__(THREADS)
 // the nine products of dbl-2008-s-1 have depth three, so lanes 0..3 take one product each per
 // level and exchange results through shared memory: 3 product latencies per doubling instead
 // of 9.  Every lane holds the full point before and after.  `sh` has 4 * F::N words.
+//
+// Quadratic extensions go one step further (dbl_coop_ext / add_coop_ext): a product over Fp2 is
+// three independent base-field products (Karatsuba), so lanes 3g .. 3g+2 take one each for
+// product g and a level costs ONE base-field product latency instead of three.  `sh` then holds
+// 12 base-field elements = 6 * F::N words.
+template <class F2>
+__device__ __forceinline__ void ext_products(const F2 &a, const F2 &b, uint32_t *sh, uint32_t lane) {
+    using B = typename F2::F;
+    constexpr int BN = F2::N / 2;
+    const uint32_t part = lane % 3u;
+    const B x = part == 0 ? a.c0 : part == 1 ? a.c1 : B::add(a.c0, a.c1);
+    const B y = part == 0 ? b.c0 : part == 1 ? b.c1 : B::add(b.c0, b.c1);
+    const B v = B::mul(x, y);
+    if (lane < 12) v.store(sh + lane * BN);
+    __syncwarp();
+}
+// product g of the last ext_products call: (v0 - NR v1) + (s - v0 - v1) u
+template <class F2>
+__device__ __forceinline__ F2 ext_result(const uint32_t *sh, int g) {
+    using B = typename F2::F;
+    constexpr int BN = F2::N / 2;
+    const B v0 = B::load(sh + (3 * g) * BN), v1 = B::load(sh + (3 * g + 1) * BN),
+            s = B::load(sh + (3 * g + 2) * BN);
+    return F2{B::sub(v0, F2::times_nr(v1)), B::sub(B::sub(s, v0), v1)};
+}
+
+template <class F>
+__device__ __forceinline__ XYZZ<F> dbl_coop_ext(const XYZZ<F> &p, uint32_t *sh, uint32_t lane) {
+    const uint32_t g = (lane / 3u) & 3u;  // product this lane works on
+    const F U = F::dbl(p.Y);
+    // level 1: V = U^2, xx = X^2
+    ext_products<F>(F::select(g == 1, p.X, U), F::select(g == 1, p.X, U), sh, lane);
+    const F V = ext_result<F>(sh, 0), xx = ext_result<F>(sh, 1);
+    __syncwarp();
+    const F M = F::add(F::dbl(xx), xx);
+    // level 2: W = U V, S = X V, M^2, ZZ' = V ZZ
+    ext_products<F>(g == 0 ? U : g == 1 ? p.X : g == 2 ? M : V,
+                    g == 0 ? V : g == 1 ? V : g == 2 ? M : p.ZZ, sh, lane);
+    const F Wv = ext_result<F>(sh, 0), S = ext_result<F>(sh, 1), MM = ext_result<F>(sh, 2),
+            ZZ3 = ext_result<F>(sh, 3);
+    __syncwarp();
+    const F X3 = F::sub(MM, F::dbl(S));
+    // level 3: M (S - X3), W Y, ZZZ' = W ZZZ
+    ext_products<F>(g == 0 ? M : Wv, g == 0 ? F::sub(S, X3) : g == 1 ? p.Y : p.ZZZ, sh, lane);
+    const F Y3 = F::sub(ext_result<F>(sh, 0), ext_result<F>(sh, 1));
+    const F ZZZ3 = ext_result<F>(sh, 2);
+    __syncwarp();
+    return XYZZ<F>{X3, Y3, ZZ3, ZZZ3};
+}
+
+// acc += q over a quadratic extension (add-2008-s in four levels, see add_coop_wide); every lane
+// holds both points; exceptional cases are uniform across the warp and take the one-lane routine
+template <class F>
+__device__ __forceinline__ void add_coop_ext(XYZZ<F> &acc, const XYZZ<F> &q, uint32_t *sh,
+                                             uint32_t lane) {
+    if (q.is_inf()) return;
+    if (acc.is_inf()) {
+        acc = q;
+        return;
+    }
+    const uint32_t g = (lane / 3u) & 3u;
+    // level 1: U1 = X1 ZZ2, S1 = Y1 ZZZ2, U2 = X2 ZZ1, S2 = Y2 ZZZ1
+    ext_products<F>(g == 0 ? acc.X : g == 1 ? acc.Y : g == 2 ? q.X : q.Y,
+                    g == 0 ? q.ZZ : g == 1 ? q.ZZZ : g == 2 ? acc.ZZ : acc.ZZZ, sh, lane);
+    const F U1 = ext_result<F>(sh, 0), S1 = ext_result<F>(sh, 1);
+    const F Pd = F::sub(ext_result<F>(sh, 2), U1), R = F::sub(ext_result<F>(sh, 3), S1);
+    __syncwarp();
+    if (Pd.is_zero()) {  // uniform
+        XYZZ<F>::add(acc, q);
+        return;
+    }
+    // level 2: PP = P^2, RR = R^2, ZZ1 ZZ2, ZZZ1 ZZZ2
+    ext_products<F>(g == 0 ? Pd : g == 1 ? R : g == 2 ? acc.ZZ : acc.ZZZ,
+                    g == 0 ? Pd : g == 1 ? R : g == 2 ? q.ZZ : q.ZZZ, sh, lane);
+    const F PP = ext_result<F>(sh, 0), RR = ext_result<F>(sh, 1), ZZ12 = ext_result<F>(sh, 2),
+            ZZZ12 = ext_result<F>(sh, 3);
+    __syncwarp();
+    // level 3: PPP = P PP, Q = U1 PP, ZZ3 = ZZ12 PP
+    ext_products<F>(g == 0 ? Pd : g == 1 ? U1 : ZZ12, PP, sh, lane);
+    const F PPP = ext_result<F>(sh, 0), Q = ext_result<F>(sh, 1), ZZ3 = ext_result<F>(sh, 2);
+    __syncwarp();
+    const F X3 = F::sub(F::sub(RR, PPP), F::dbl(Q));
+    // level 4: R (Q - X3), S1 PPP, ZZZ3 = ZZZ12 PPP
+    ext_products<F>(g == 0 ? R : g == 1 ? S1 : ZZZ12, g == 0 ? F::sub(Q, X3) : PPP, sh, lane);
+    acc.X = X3;
+    acc.Y = F::sub(ext_result<F>(sh, 0), ext_result<F>(sh, 1));
+    acc.ZZ = ZZ3;
+    acc.ZZZ = ext_result<F>(sh, 2);
+    __syncwarp();
+}
+
 template <class F>
 __device__ __forceinline__ XYZZ<F> dbl_coop(const XYZZ<F> &p, uint32_t *sh, uint32_t lane) {
+    if constexpr (BaseLimbs<F>::EXT) return dbl_coop_ext<F>(p, sh, lane);
     const uint32_t slot = (lane & 3u) * F::N;
     const F U = F::dbl(p.Y);
     // level 1: V = U^2, xx = X^2
@@ -632,7 +724,7 @@ __global__ void __launch_bounds__(32) k_final(const uint32_t *__restrict__ windo
     using R = Raw<C>;
     using F = typename C::Fq;
     using X = XYZZ<F>;
-    __shared__ __align__(16) uint32_t sh[4 * F::N];
+    __shared__ __align__(16) uint32_t sh[6 * F::N];
     constexpr bool WIDE = CoopField<F>::OK;
     __shared__ uint32_t win[CoopField<F>::WIN_WORDS];
     if (blockIdx.x != 0) return;
@@ -650,6 +742,8 @@ __global__ void __launch_bounds__(32) k_final(const uint32_t *__restrict__ windo
         X q = X::load(window_sums + (size_t)w * R::XW);
         if constexpr (WIDE)
             add_coop_wide<F>(r, q, sh, win, lane);
+        else if constexpr (BaseLimbs<F>::EXT)
+            add_coop_ext<F>(r, q, sh, lane);
         else
             X::add(r, q);
     }
@@ -674,7 +768,7 @@ __global__ void __launch_bounds__(32)
     using R = Raw<C>;
     using F = typename C::Fq;
     using X = XYZZ<F>;
-    __shared__ __align__(16) uint32_t sh[4 * F::N];
+    __shared__ __align__(16) uint32_t sh[6 * F::N];
     if (blockIdx.x != 0) return;
     const uint32_t lane = threadIdx.x & 31;
     X run = X::inf(), acc = X::inf(), sumS = X::inf();
