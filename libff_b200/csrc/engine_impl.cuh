@@ -31,7 +31,9 @@ uint32_t pick_window_bits(const Ctx &ctx, size_t n) {
     uint32_t best_c = 2;
     for (uint32_t c = 2; c <= 22; c++) {
         double W = (double)((bits + 1 + c - 1) / c);
-        double cost = (double)n * W * 10.0 + W * (double)(1u << (c - 1)) * 53.0;
+        // (quadratic extensions: 40 -- measured at 2^20, profiles/segment_window_sweep_r01e.log)
+        const double bucket_cost = BaseLimbs<typename C::Fq>::EXT ? 40.0 : 53.0;
+        double cost = (double)n * W * 10.0 + W * (double)(1u << (c - 1)) * bucket_cost;
         if (c == 2 || cost < best) best = cost, best_c = c;
     }
     return best_c;
@@ -141,10 +143,18 @@ inline uint32_t pick_carry_segment(const Ctx &ctx) {
 
 // Sorted entries per thread in the first accumulation round: long segments amortise the carry
 // rounds (one full addition per segment), short ones keep all SMs busy on small inputs.
+// Measured (profiles/segment_window_sweep_r01e.log): prime fields gain from 128-entry segments
+// when enough threads remain (alt_bn128 G1 2^22: 12.9 -> 12.5 ms, 2^24: 42.6 -> 42.3); the 24-limb
+// field, whose carry rounds are the most expensive and whose kernel holds only 256 threads per SM,
+// wants them even below one wave (bw6_761 2^19: 46.2 -> 42.3 ms, 2^17: 21.1 -> 19.0); quadratic
+// extensions lose with more than 64.
+template <class C>
 inline uint32_t pick_segment(const Ctx &ctx, size_t total) {
     if (ctx.opt_segment > 0) return ((uint32_t)ctx.opt_segment + 3u) & ~3u;  // uint4 item loads
-    const size_t want_threads = 148 * 384 * 4;
-    uint32_t seg = 64;
+    constexpr bool ext = BaseLimbs<typename C::Fq>::EXT;
+    constexpr int limbs = BaseLimbs<typename C::Fq>::N;
+    const size_t want_threads = (!ext && limbs >= 24) ? 148 * 128 : 148 * 384 * 4;
+    uint32_t seg = ext ? 64 : 128;
     while (seg > 8 && total / seg < want_threads) seg >>= 1;
     return seg;
 }
@@ -227,7 +237,7 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
     // windows (bucket sets) that hold items
     // (an earlier range may have used higher windows than this one: meta[1] is cumulative)
     const int Wu = pre ? 1 : std::max<int>(1, std::min<int>(W, (int)meta[1]));
-    const uint32_t seg = pick_segment(ctx, total);
+    const uint32_t seg = pick_segment<C>(ctx, total);
     const size_t t1 = ((size_t)total + seg - 1) / seg;
     uint32_t *seg_bucket;
     if (!reserve_as(ctx, SL_SEG_BUCKET, (t1 + 1) * 4, &seg_bucket)) return false;
