@@ -43,11 +43,11 @@ MIN_BYTES = {0: 96, 1: 160, 2: 128, 3: 240, 4: 224, 5: 240, 6: 128, 7: 224}
 
 # ncu --set full, k_accum_first, per launch: 28.72 GB read + 1.28 GB written
 # (profiles/accum_first_r01d_raw.csv)
-NCU_TRAFFIC = {("alt_bn128_g1", 1 << 24): 30.00e9, ("bls12_377_g1", 1 << 22): 11.31e9,
+NCU_TRAFFIC = {("alt_bn128_g1", 1 << 24): 29.85e9, ("bls12_377_g1", 1 << 22): 11.31e9,
                ("alt_bn128_g2", 1 << 20): 2.68e9, ("bw6_761_g1", 1 << 19): 6.18e9}
 # sm__pipe_fmaheavy_cycles_active (the pipe IMAD / IMAD.WIDE issue on) of k_accum_first in the
 # committed `ncu --set full` captures: the hardware-side utilisation figure next to `frac`
-NCU_PIPE_UTIL = {("alt_bn128_g1", 1 << 24): (0.897, "profiles/accum_first_r01d_raw.csv"),
+NCU_PIPE_UTIL = {("alt_bn128_g1", 1 << 24): (0.894, "profiles/accum_first_r01e_raw.csv"),
                  ("bls12_377_g1", 1 << 22): (0.749, "profiles/accum_first_bls12_377_g1_r01e_raw.csv"),
                  ("alt_bn128_g2", 1 << 20): (0.670, "profiles/accum_first_alt_bn128_g2_r01e_raw.csv"),
                  ("bw6_761_g1", 1 << 19): (0.641, "profiles/accum_first_bw6_761_g1_r01e_raw.csv")}
@@ -329,7 +329,7 @@ def main():
         "pipe_utilisation_ncu": dict(zip(("fmaheavy_cycles_active", "source"),
                                          NCU_PIPE_UTIL.get((args.group, n), (None, None)))),
         # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the committed
-        # `ncu --set full` capture of this workload (profiles/accum_first_r01d_raw.csv)
+        # `ncu --set full` capture of this workload (profiles/accum_first*_r01e_raw.csv)
         "traffic": NCU_TRAFFIC.get((args.group, n)),
         "traffic_unit": "bytes per launch (ncu dram read + write); algorithmic gather = items x "
                         "(affine point + 4-byte item)",
