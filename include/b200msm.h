@@ -172,7 +172,10 @@ bool b200msm_stream_finish(uint64_t stream, void *out, size_t out_bytes);
  * option: "window_bits" (0 = automatic), "segment" (entries per thread of the accumulation),
  * "h2d_parts" (point ranges a host-buffer multi_exp is cut into so that uploads overlap the
  * computation; 0 = automatic, 1 = no overlap), "h2d_growth" (size ratio of consecutive ranges in
- * percent; 0 = 130), "window_groups" (groups the windows are walked in, top window first, so that
+ * percent; 0 = automatic), "h2d_shared_buckets" (1, default: the ranges are sorted with the digit
+ * size of the whole call and accumulate into one bucket set that is reduced once; 0: one
+ * independent MSM per range), "trace" (1: per-range phase times of a pipelined call on stderr; it
+ * serialises the pipeline), "window_groups" (groups the windows are walked in, top window first, so that
  * the reduction of one group runs under the accumulation of the next; 0 = automatic, 1 = one
  * group), "carry_segment" (carries per thread in the later accumulation rounds; 0 = 4),
  * "reduce_chunk" (log2 of the buckets per thread in the bucket reduction; 0 = automatic). */

@@ -112,12 +112,15 @@ B200_DEV void row_acc_shift_from(uint32_t *acc, const uint32_t *a, uint32_t bi) 
 
 }  // namespace limb
 
-// CALL_MIN: fields of at least this many limbs call one shared copy of the product (see
-// B200_CALL_MIN_LIMBS); kernels pick the policy per use through Rebind (fp2.cuh): the layout of
-// an element does not depend on it.
+// CALL_MIN > 0: fields of at least this many limbs call one shared copy of the product (see
+// B200_CALL_MIN_LIMBS).  CALL_MIN < 0: fields of at least -CALL_MIN limbs inline a ROLLED product
+// (row pairs in a loop) -- small code without the call.  Kernels pick the policy per use through
+// Rebind (fp2.cuh): the layout of an element does not depend on it.
 template <class P, int CALL_MIN = B200_CALL_MIN_LIMBS>
 struct Fp {
     static constexpr int N = P::N;
+    static constexpr bool ROLLED = CALL_MIN < 0 && N >= -CALL_MIN;
+    static constexpr bool CALLS = CALL_MIN > 0 && N >= CALL_MIN;
     using Params = P;
     // The squaring rows and the shared-reduction product accumulate up to 3p before the shift,
     // which needs p < 2^(32 N - 2); every coordinate field here has the two spare bits, the
@@ -320,10 +323,30 @@ struct Fp {
     // product (a 24-limb product is ~1300 instructions; inlining a dozen per group operation
     // only thrashes the instruction cache and the compiler).
     B200_DEV static Fp mul(const Fp &a, const Fp &b) {
-        if constexpr (N >= CALL_MIN)
+        if constexpr (ROLLED)
+            return mul_rolled(a, b);
+        else if constexpr (CALLS)
             return mul_call(a, b);
         else
             return mul_inline(a, b);
+    }
+    // The same product with the row pairs in a loop (first pair peeled): a third of the code of
+    // the fully unrolled form.  The multiplier's limbs rotate through registers so that every
+    // index stays static.
+    B200_DEV static Fp mul_rolled(const Fp &a, const Fp &b) {
+        uint32_t E[N], O[N], bb[N];
+#pragma unroll
+        for (int i = 0; i < N; i++) bb[i] = b.v[i];
+        mont_row(E, O, a.v, bb[0], true);
+        mont_row(O, E, a.v, bb[1], false);
+#pragma unroll 1
+        for (int it = 1; it < N / 2; it++) {
+#pragma unroll
+            for (int k = 0; k + 2 < N; k++) bb[k] = bb[k + 2];
+            mont_row(E, O, a.v, bb[0], false);
+            mont_row(O, E, a.v, bb[1], false);
+        }
+        return finish(E, O);
     }
     __device__ __noinline__ static Fp mul_call(const Fp &a, const Fp &b) { return mul_inline(a, b); }
     B200_DEV static Fp mul_inline(const Fp &a, const Fp &b) {
@@ -340,7 +363,7 @@ struct Fp {
     B200_DEV static Fp sqr(const Fp &a) {
         if constexpr (!SPARE2)
             return mul(a, a);
-        else if constexpr (N >= CALL_MIN)
+        else if constexpr (CALLS)
             return sqr_call(a);
         else
             return sqr_inline(a);
@@ -362,10 +385,27 @@ struct Fp {
     B200_DEV static Fp mul2(const Fp &a, const Fp &b, const Fp &c, const Fp &d) {
         if constexpr (!SPARE2)
             return add(mul(a, b), mul(c, d));
-        else if constexpr (N >= CALL_MIN)
+        else if constexpr (ROLLED)
+            return mul2_rolled(a, b, c, d);
+        else if constexpr (CALLS)
             return mul2_call(a, b, c, d);
         else
             return mul2_inline(a, b, c, d);
+    }
+    B200_DEV static Fp mul2_rolled(const Fp &a, const Fp &b, const Fp &c, const Fp &d) {
+        uint32_t E[N], O[N], bb[N], dd[N];
+#pragma unroll
+        for (int i = 0; i < N; i++) bb[i] = b.v[i], dd[i] = d.v[i];
+        mont_row2(E, O, a.v, bb[0], c.v, dd[0], true);
+        mont_row2(O, E, a.v, bb[1], c.v, dd[1], false);
+#pragma unroll 1
+        for (int it = 1; it < N / 2; it++) {
+#pragma unroll
+            for (int k = 0; k + 2 < N; k++) bb[k] = bb[k + 2], dd[k] = dd[k + 2];
+            mont_row2(E, O, a.v, bb[0], c.v, dd[0], false);
+            mont_row2(O, E, a.v, bb[1], c.v, dd[1], false);
+        }
+        return finish(E, O);
     }
     __device__ __noinline__ static Fp mul2_call(const Fp &a, const Fp &b, const Fp &c, const Fp &d) {
         return mul2_inline(a, b, c, d);

@@ -110,16 +110,41 @@ struct BaseLimbs<Fp2<P, NR, X>> {
 #ifndef B200_TAIL_CALL_MIN_LIMBS
 #define B200_TAIL_CALL_MIN_LIMBS 12
 #endif
+#ifndef B200_TAIL_ROLLED_MIN_LIMBS
+// prime fields from this many limbs inline the ROLLED product instead: faster again than the call
+// (bw6_761 2^19: 34.8 -> 33.8 ms, bls12_377 G1 2^22: 32.5 -> 32.1 ms)
+#define B200_TAIL_ROLLED_MIN_LIMBS 12
+#endif
 template <class F>
-using TailField = typename Rebind<F, (BaseLimbs<F>::N >= B200_CALL_MIN_LIMBS         ? B200_CALL_MIN_LIMBS
+using TailField = typename Rebind<F, ((!BaseLimbs<F>::EXT && BaseLimbs<F>::N >= B200_TAIL_ROLLED_MIN_LIMBS)
+                                          ? -BaseLimbs<F>::N
+                                      : BaseLimbs<F>::N >= B200_CALL_MIN_LIMBS      ? B200_CALL_MIN_LIMBS
                                       : BaseLimbs<F>::N >= B200_TAIL_CALL_MIN_LIMBS ? B200_TAIL_CALL_MIN_LIMBS
                                                                                     : B200_CALL_MIN_LIMBS)>::type;
 // The accumulation kernel inlines the products of 12-limb prime fields (calls cost 28.5 -> 37.8 ms
 // there) but calls them for the 12-limb quadratic extensions (38.3 -> 33.6 ms: three base-field
 // products per product no longer fit the instruction cache).
+// ... and rolls them (Fp::mul_rolled) where measured faster: bls12_377 Fq, whose fully unrolled
+// kernel is 171 KB and instruction-fetch bound (2^22: accumulation 28.9 -> 25.9 ms); the equally
+// wide bls12_381 Fq runs at 85 % of the pipe unrolled and loses 3 % rolled, so it stays unrolled.
+template <class P>
+struct AccumRolled {
+    static constexpr bool value = false;
+};
+template <>
+struct AccumRolled<Bls12377FqParams> {
+    static constexpr bool value = true;
+};
+// bw6_761 Fq (24 limbs): the rolled inline product also beats the call, whose operands travel
+// through the stack (2^19: accumulation 30.5 -> 25.5 ms, stack frame 1792 -> 688 bytes).
+template <>
+struct AccumRolled<Bw6761FqParams> {
+    static constexpr bool value = true;
+};
 template <class F>
-using AccumField = typename Rebind<F, (BaseLimbs<F>::EXT && BaseLimbs<F>::N >= 12
-                                           ? 12
+using AccumField = typename Rebind<F, (BaseLimbs<F>::EXT && BaseLimbs<F>::N >= 12 ? 12
+                                       : (!BaseLimbs<F>::EXT && AccumRolled<typename F::Params>::value)
+                                           ? -BaseLimbs<F>::N
                                            : B200_CALL_MIN_LIMBS)>::type;
 
 }  // namespace b200msm
