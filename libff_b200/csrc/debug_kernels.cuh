@@ -21,6 +21,11 @@ enum DebugOp {
     DBG_G_MADD = 12,   // b must be special (Z = 1) or zero
     DBG_G_NEG = 13,
     DBG_FQ_MUL2 = 14,  // a b + (a + b)(a - b) through the shared-reduction product
+    // the other code shapes of the same product (fp.cuh CALL_MIN policies): bit for bit equal
+    DBG_FQ_MUL_ROLLED = 15,
+    DBG_FQ_MUL2_ROLLED = 16,
+    DBG_FQ_MUL_CALLED = 17,
+    DBG_FQ_SQR_CALLED = 18,
 };
 
 template <class C>
@@ -32,7 +37,19 @@ __global__ void k_debug_op(int op, const uint32_t *__restrict__ a, const uint32_
     using X = XYZZ<F>;
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    if (op <= DBG_FQ_INV || op == DBG_FQ_MUL_D || op == DBG_FQ_MUL2) {
+    if (op >= DBG_FQ_MUL_ROLLED && op <= DBG_FQ_SQR_CALLED) {
+        using FR = typename Rebind<F, -1>::type;  // every product rolled
+        using FC = typename Rebind<F, 1>::type;   // every product a call
+        if (op == DBG_FQ_MUL_ROLLED || op == DBG_FQ_MUL2_ROLLED) {
+            const FR x = FR::load(a + (size_t)i * F::N), y = FR::load(b + (size_t)i * F::N);
+            const FR r = op == DBG_FQ_MUL_ROLLED ? FR::mul(x, y) : FR::mul2(x, y, FR::add(x, y), FR::sub(x, y));
+            r.store(out + (size_t)i * F::N);
+        } else {
+            const FC x = FC::load(a + (size_t)i * F::N);
+            const FC r = op == DBG_FQ_MUL_CALLED ? FC::mul(x, FC::load(b + (size_t)i * F::N)) : FC::sqr(x);
+            r.store(out + (size_t)i * F::N);
+        }
+    } else if (op <= DBG_FQ_INV || op == DBG_FQ_MUL_D || op == DBG_FQ_MUL2) {
         F x = F::load(a + (size_t)i * F::N), y = F::zero(), r;
         if (op <= DBG_FQ_MUL || op == DBG_FQ_MUL_D || op == DBG_FQ_MUL2) y = F::load(b + (size_t)i * F::N);
         switch (op) {

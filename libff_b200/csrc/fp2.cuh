@@ -141,8 +141,11 @@ template <>
 struct AccumRolled<Bw6761FqParams> {
     static constexpr bool value = true;
 };
+#ifndef B200_ACCUM_EXT12_POLICY
+#define B200_ACCUM_EXT12_POLICY 12   // 12-limb quadratic extensions: call (12) or roll (-12)
+#endif
 template <class F>
-using AccumField = typename Rebind<F, (BaseLimbs<F>::EXT && BaseLimbs<F>::N >= 12 ? 12
+using AccumField = typename Rebind<F, (BaseLimbs<F>::EXT && BaseLimbs<F>::N >= 12 ? B200_ACCUM_EXT12_POLICY
                                        : (!BaseLimbs<F>::EXT && AccumRolled<typename F::Params>::value)
                                            ? -BaseLimbs<F>::N
                                            : B200_CALL_MIN_LIMBS)>::type;

@@ -92,6 +92,35 @@ def test_shared_reduction_product_and_squaring(engine, ref, gid):
                                   ref.field_op(fid, ref.OP_SQR, a))
 
 
+@pytest.mark.parametrize("gid", GROUPS)
+def test_product_code_shapes_agree(engine, ref, gid):
+    """The Montgomery product exists in three code shapes chosen per kernel (fp.cuh CALL_MIN:
+    fully unrolled, rolled row pairs, one shared called copy); each must give the reference's
+    product (fp.tcc:50-228) bit for bit, incl. 0, 1 and p-1 operands, also through the
+    shared-reduction form a b + c d and the dedicated squaring."""
+    fid = ref.FQ_OF_GROUP[gid]
+    n = 2051
+    a = rand_field(ref, fid, n, 31)
+    b = rand_field(ref, fid, n, 32)
+    one = _one(ref, fid)[0]
+    minus_one = ref.field_op(fid, ref.OP_NEG, _one(ref, fid))[0]
+    a[0] = 0
+    b[1] = 0
+    b[2] = a[2]
+    a[3], b[3] = minus_one, minus_one
+    a[4], b[4] = minus_one, one
+    a[5] = one
+    prod = ref.field_op(fid, ref.OP_MUL, a, b)
+    np.testing.assert_array_equal(engine.debug_op(gid, engine.FQ_MUL_ROLLED, a, b), prod)
+    np.testing.assert_array_equal(engine.debug_op(gid, engine.FQ_MUL_CALLED, a, b), prod)
+    np.testing.assert_array_equal(engine.debug_op(gid, engine.FQ_SQR_CALLED, a, b),
+                                  ref.field_op(fid, ref.OP_SQR, a))
+    want2 = ref.field_op(fid, ref.OP_ADD, prod,
+                         ref.field_op(fid, ref.OP_MUL, ref.field_op(fid, ref.OP_ADD, a, b),
+                                      ref.field_op(fid, ref.OP_SUB, a, b)))
+    np.testing.assert_array_equal(engine.debug_op(gid, engine.FQ_MUL2_ROLLED, a, b), want2)
+
+
 def _one(ref, fid):
     """Montgomery one of field fid as a (1, words) array (Fq2: (1, 0))."""
     words = ref.lib().ref_field_bytes(fid) // 8
