@@ -142,10 +142,13 @@ struct AccumRolled<Bw6761FqParams> {
     static constexpr bool value = true;
 };
 #ifndef B200_ACCUM_EXT12_POLICY
-#define B200_ACCUM_EXT12_POLICY 12   // 12-limb quadratic extensions: call (12) or roll (-12)
+// 12-limb quadratic extensions call the base-field product (12) unless the modulus is marked
+// AccumRolled: bls12_377 Fq2 rolled 43.4 -> 42.1 ms at 2^20 (accumulation 31.2 -> 29.9)
+#define B200_ACCUM_EXT12_POLICY 12
 #endif
 template <class F>
-using AccumField = typename Rebind<F, (BaseLimbs<F>::EXT && BaseLimbs<F>::N >= 12 ? B200_ACCUM_EXT12_POLICY
+using AccumField = typename Rebind<F, (BaseLimbs<F>::EXT && BaseLimbs<F>::N >= 12
+                                           ? (AccumRolled<typename F::Params>::value ? -12 : B200_ACCUM_EXT12_POLICY)
                                        : (!BaseLimbs<F>::EXT && AccumRolled<typename F::Params>::value)
                                            ? -BaseLimbs<F>::N
                                            : B200_CALL_MIN_LIMBS)>::type;
