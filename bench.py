@@ -43,14 +43,14 @@ MIN_BYTES = {0: 96, 1: 160, 2: 128, 3: 240, 4: 224, 5: 240, 6: 128, 7: 224}
 
 # ncu --set full, k_accum_first, per launch: 28.72 GB read + 1.28 GB written
 # (profiles/accum_first_r01d_raw.csv)
-NCU_TRAFFIC = {("alt_bn128_g1", 1 << 24): 29.85e9, ("bls12_377_g1", 1 << 22): 11.31e9,
-               ("alt_bn128_g2", 1 << 20): 2.68e9, ("bw6_761_g1", 1 << 19): 6.18e9}
+NCU_TRAFFIC = {("alt_bn128_g1", 1 << 24): 29.85e9, ("bls12_377_g1", 1 << 22): 11.01e9,
+               ("alt_bn128_g2", 1 << 20): 2.64e9, ("bw6_761_g1", 1 << 19): 2.02e9}
 # sm__pipe_fmaheavy_cycles_active (the pipe IMAD / IMAD.WIDE issue on) of k_accum_first in the
 # committed `ncu --set full` captures: the hardware-side utilisation figure next to `frac`
 NCU_PIPE_UTIL = {("alt_bn128_g1", 1 << 24): (0.894, "profiles/accum_first_r01e_raw.csv"),
-                 ("bls12_377_g1", 1 << 22): (0.749, "profiles/accum_first_bls12_377_g1_r01e_raw.csv"),
-                 ("alt_bn128_g2", 1 << 20): (0.670, "profiles/accum_first_alt_bn128_g2_r01e_raw.csv"),
-                 ("bw6_761_g1", 1 << 19): (0.641, "profiles/accum_first_bw6_761_g1_r01e_raw.csv")}
+                 ("bls12_377_g1", 1 << 22): (0.831, "profiles/accum_first_bls12_377_g1_r01f_raw.csv"),
+                 ("alt_bn128_g2", 1 << 20): (0.677, "profiles/accum_first_alt_bn128_g2_r01f_raw.csv"),
+                 ("bw6_761_g1", 1 << 19): (0.626, "profiles/accum_first_bw6_761_g1_r01f_raw.csv")}
 
 
 def executed_macs_per_item(gid):
