@@ -29,6 +29,11 @@ namespace b200msm {
 #define B200_DEV __device__ __forceinline__
 // Fields of at least this many 32-bit limbs call one shared copy of the Montgomery product
 // instead of inlining it at every use (instruction-cache footprint against call overhead).
+// Squaring of a 24-limb field under the rolled policy: 0 = dedicated squaring inlined (unrolled),
+// 1 = the same as one shared called copy, 2 = the rolled product a * a
+#ifndef B200_ROLLED_SQR_POLICY
+#define B200_ROLLED_SQR_POLICY 0
+#endif
 #ifndef B200_CALL_MIN_LIMBS
 #define B200_CALL_MIN_LIMBS 24
 #endif
@@ -363,7 +368,9 @@ struct Fp {
     B200_DEV static Fp sqr(const Fp &a) {
         if constexpr (!SPARE2)
             return mul(a, a);
-        else if constexpr (CALLS)
+        else if constexpr (ROLLED && N >= 24 && B200_ROLLED_SQR_POLICY == 2)
+            return mul_rolled(a, a);
+        else if constexpr (CALLS || (ROLLED && N >= 24 && B200_ROLLED_SQR_POLICY == 1))
             return sqr_call(a);
         else
             return sqr_inline(a);
