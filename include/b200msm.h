@@ -60,6 +60,20 @@ extern "C" {
  * pool; idempotent for the same device.  Mirrors <curve>_init() (ffi/ffi.cpp:124-128,194-198):
  * call once before anything else, not thread-safe. */
 bool b200msm_init(int device);
+/* The same for several GPUs of one box (b200msm_init(num_gpus)): `count` device
+ * ordinals, one engine context each.  From then on multi_exp / multi_exp_resident[_bases] /
+ * multi_exp_precomputed cut their index range into one contiguous range per device exactly as
+ * the reference cuts it into `chunks` for its OpenMP threads -- one = n / count, the last range
+ * takes the remainder (multiexp.tcc:655-678; n < count or count == 1: a single range) -- run the
+ * ranges concurrently, one host thread per device, and add the partial points on the first
+ * device (multiexp.tcc:681-685).  batch_exp and batch_to_special shard by output range with no
+ * exchange.  The wire-format, streamed and debug entry points use the first device only.
+ * A device may be listed more than once (two independent contexts on one GPU; a test aid).
+ * init_all binds every visible device and returns their number (0 on failure).
+ * Option "num_gpus" (b200msm_set_option) limits later calls to the first k bound devices. */
+bool b200msm_init_devices(const int *devices, size_t count);
+int b200msm_init_all(void);
+size_t b200msm_device_count(void);
 void b200msm_shutdown(void);
 const char *b200msm_last_error(void);
 
@@ -83,6 +97,11 @@ bool b200msm_scalars_upload(uint32_t group, const void *scalars, size_t scalars_
                             uint64_t *handle);
 bool b200msm_multi_exp_resident(uint32_t group, uint64_t bases_handle, uint64_t scalars_handle,
                                 size_t first, size_t n, void *out, size_t out_bytes);
+/* The prover's shape of the call: the bases (a proving key) stay resident, the scalars (a
+ * witness) come from the host with every call and are uploaded in ranges under the computation.
+ * n must equal the number of resident bases. */
+bool b200msm_multi_exp_resident_bases(uint32_t group, uint64_t bases_handle, const void *scalars,
+                                      size_t scalars_bytes, size_t n, void *out, size_t out_bytes);
 bool b200msm_release(uint64_t handle);
 
 /* The same MSM on the byte format of the reference's C ABI (ffi/ffi_serialization.hpp:12-16,
@@ -90,10 +109,12 @@ bool b200msm_release(uint64_t handle);
  * every base-field value big-endian, left-padded to the in-memory width, plain (not Montgomery);
  * Fq2 as c1 | c0; a point is affine X | Y (b200msm_wire_point_bytes(group) bytes: 64 / 128 / 96 /
  * 192) with (0, 1) for infinity; a scalar is sizeof(Fr) bytes.  Decoding, validation and encoding
- * run on the device.  Like the reference's readers the call fails when a value is >= its modulus;
- * flags add the point checks of group_element_read (ffi_serialization.tcc:165). */
-#define B200MSM_WIRE_CHECK_CURVE 1u    /* is_well_formed(): y^2 = x^3 + b */
-#define B200MSM_WIRE_CHECK_SUBGROUP 2u /* is_in_safe_subgroup(): r P = 0 (n scalar multiplications) */
+ * run on the device.  Like the reference's readers the call fails when a value is >= its modulus
+ * or a point fails is_well_formed() (y^2 = x^3 + b) or is_in_safe_subgroup() (r P = 0) -- both
+ * checks of group_element_read (ffi_serialization.tcc:165) run by default (flags = 0).  A caller
+ * that has validated its points before may opt out of either: */
+#define B200MSM_WIRE_SKIP_CURVE_CHECK 1u    /* trust y^2 = x^3 + b */
+#define B200MSM_WIRE_SKIP_SUBGROUP_CHECK 2u /* trust r P = 0 (saves n scalar multiplications) */
 size_t b200msm_wire_point_bytes(uint32_t group);
 bool b200msm_multi_exp_wire(uint32_t group, const void *points, size_t points_bytes,
                             const void *scalars, size_t scalars_bytes, size_t n, uint32_t flags,
@@ -117,6 +138,31 @@ bool b200msm_batch_exp(uint32_t group, size_t scalar_bits, size_t window,
                        const void *const *table_rows, size_t num_rows, size_t row_len,
                        const void *scalars, size_t scalars_bytes, size_t n, void *out,
                        size_t out_bytes);
+/* libff::batch_exp_with_coeff<G, Fr>(scalar_size, window, table, coeff, v) (multiexp.tcc:917-947):
+ * out[i] = (coeff * v[i]) g; `coeff` is one Fr element (Montgomery form), or NULL for batch_exp. */
+bool b200msm_batch_exp_with_coeff(uint32_t group, size_t scalar_bits, size_t window,
+                                  const void *const *table_rows, size_t num_rows, size_t row_len,
+                                  const void *coeff, size_t coeff_bytes, const void *scalars,
+                                  size_t scalars_bytes, size_t n, void *out, size_t out_bytes);
+/* Fixed-base window tables kept resident (normalised once, replicated on every bound device):
+ * table_upload takes a window_table<G> the host already has (get_window_table, multiexp.tcc:
+ * 809-846); table_build is get_window_table itself on the device from the base g (one GroupT
+ * element): entry [r][j] = j 2^(r window) g, the last row shorter (:815) with a zero tail;
+ * table_download returns the table (special form, Z = 1) into caller-owned rows so that the
+ * reference's own consumers of a window_table keep working; batch_exp_resident is batch_exp /
+ * batch_exp_with_coeff (coeff != NULL) from the resident table.  Release with b200msm_release. */
+bool b200msm_table_upload(uint32_t group, size_t scalar_bits, size_t window,
+                          const void *const *table_rows, size_t num_rows, size_t row_len,
+                          uint64_t *handle);
+bool b200msm_table_build(uint32_t group, size_t scalar_bits, size_t window, const void *g,
+                         size_t g_bytes, uint64_t *handle);
+bool b200msm_table_shape(uint64_t handle, size_t *scalar_bits, size_t *window, size_t *num_rows,
+                         size_t *row_len);
+bool b200msm_table_download(uint64_t handle, void *const *table_rows, size_t num_rows,
+                            size_t row_len);
+bool b200msm_batch_exp_resident(uint32_t group, uint64_t table_handle, const void *scalars,
+                                size_t scalars_bytes, size_t n, const void *coeff,
+                                size_t coeff_bytes, void *out, size_t out_bytes);
 
 /* Element-wise leaves of the path, for parity tests (n elements each, same layout as above):
  * op 0..5 coordinate field add, sub, mul, sqr, neg, inverse (Fp_model, fields/fp.tcc:50-727;
@@ -140,7 +186,11 @@ bool b200msm_debug_op(uint32_t group, uint32_t op, const void *a, const void *b,
  *                      (scalars_handle == 0: n * sizeof(Fr) bytes, Montgomery form).
  * Where W c equals the scalar width the reference drops the carry out of the top signed digit
  * (field_utils.tcc:205-239); here such scalars are folded to r - s, so the result is always
- * the group element sum s_i P_i. */
+ * the group element sum s_i P_i.  A streamed MSM begun with B200MSM_STREAM_REFERENCE_CARRY or'ed
+ * into precompute_c reproduces the reference instead: its signed recoding (a digit of exactly
+ * 2^(c-1) carries) with the top carry dropped, bit for bit what multi_exp_stream_with_precompute
+ * returns. */
+#define B200MSM_STREAM_REFERENCE_CARRY 0x100u
 uint32_t b200msm_precompute_window_bits(uint32_t group, size_t n);
 size_t b200msm_precompute_digits(uint32_t group, uint32_t c);
 bool b200msm_precompute(uint32_t group, uint64_t bases_handle, uint32_t c, uint64_t *table_handle);
@@ -178,13 +228,20 @@ bool b200msm_stream_finish(uint64_t stream, void *out, size_t out_bytes);
  * serialises the pipeline), "window_groups" (groups the windows are walked in, top window first, so that
  * the reduction of one group runs under the accumulation of the next; 0 = automatic, 1 = one
  * group), "carry_segment" (carries per thread in the later accumulation rounds; 0 = 4),
- * "reduce_chunk" (log2 of the buckets per thread in the bucket reduction; 0 = automatic). */
+ * "reduce_chunk" (log2 of the buckets per thread in the bucket reduction; 0 = automatic),
+ * "num_gpus" (bound devices a call spreads over; 0 = all), "h2d_pack" (special-form bases leave
+ * their constant Z behind on upload: 0 never, 1 pageable sources (default), 2 always),
+ * "sort_overlap" (groups of windows whose counting sort runs under the previous group's
+ * accumulation; 0 = automatic, 1 = one sort for all windows), "coop_accum" (lane-cooperative
+ * bucket accumulation of the wide fields: 0 automatic, 1 off, 2 on). */
 bool b200msm_set_option(const char *name, int64_t value);
 /* CUDA-event timings (ms) of the phases of the most recent multi_exp on this thread's engine,
  * measured on the engine's own stream.  Writes up to `cap` values, returns how many phases exist.
  * Order: 0 upload/ingest, 1 digits+histogram, 2 scan, 3 scatter, 4 bucket accumulation
  * (first round), 5 carry rounds, 6 bucket reduction, 7 window reduction + final, 8 total. */
 size_t b200msm_last_timings(float *ms, size_t cap);
+/* the same for one bound device (last_timings is the element-wise maximum over the devices) */
+size_t b200msm_device_timings(size_t device_index, float *ms, size_t cap);
 const char *b200msm_timing_name(size_t phase);
 /* Device-side stopwatch for benchmarks: CUDA events recorded on the engine's own stream (the
  * stream every kernel and copy of this library is issued on).  timer_stop waits for the stop

@@ -34,7 +34,9 @@ __all__ = [
     "precompute_window_bits", "MsmStream", "STREAM_MEMORY_SPECIAL", "STREAM_MEMORY_NORMAL",
     "STREAM_BINARY_PLAIN", "STREAM_BINARY_MONTGOMERY",
     "set_option", "window_bits", "shard_range", "multi_exp_wire", "wire_point_bytes",
-    "WIRE_CHECK_CURVE", "WIRE_CHECK_SUBGROUP",
+    "WIRE_SKIP_CURVE_CHECK", "WIRE_SKIP_SUBGROUP_CHECK", "init_devices", "init_all",
+    "device_count", "multi_exp_resident_bases", "batch_exp_with_coeff", "WindowTable",
+    "STREAM_REFERENCE_CARRY", "device_timings",
 ]
 
 ALT_BN128_G1, ALT_BN128_G2, BLS12_377_G1, BW6_761_G1 = 0, 1, 2, 3
@@ -54,6 +56,10 @@ ABI_SYMBOLS = [
     "b200msm_timer_stop", "b200msm_precompute_window_bits", "b200msm_precompute_digits",
     "b200msm_precompute", "b200msm_precomputed_upload", "b200msm_multi_exp_precomputed",
     "b200msm_stream_begin", "b200msm_stream_push", "b200msm_stream_finish",
+    "b200msm_init_devices", "b200msm_init_all", "b200msm_device_count",
+    "b200msm_multi_exp_resident_bases", "b200msm_batch_exp_with_coeff", "b200msm_table_upload",
+    "b200msm_table_build", "b200msm_table_shape", "b200msm_table_download",
+    "b200msm_batch_exp_resident", "b200msm_device_timings",
 ]
 
 
@@ -115,6 +121,19 @@ def load():
         "b200msm_stream_finish": (C.c_bool, [u64, vp, sz]),
         "b200msm_timer_start": (C.c_bool, []),
         "b200msm_timer_stop": (C.c_float, []),
+        "b200msm_init_devices": (C.c_bool, [C.POINTER(C.c_int), sz]),
+        "b200msm_init_all": (C.c_int, []),
+        "b200msm_device_count": (sz, []),
+        "b200msm_multi_exp_resident_bases": (C.c_bool, [u32, u64, vp, sz, sz, vp, sz]),
+        "b200msm_batch_exp_with_coeff": (C.c_bool, [u32, sz, sz, C.POINTER(vp), sz, sz, vp, sz, vp,
+                                                    sz, sz, vp, sz]),
+        "b200msm_table_upload": (C.c_bool, [u32, sz, sz, C.POINTER(vp), sz, sz, C.POINTER(u64)]),
+        "b200msm_table_build": (C.c_bool, [u32, sz, sz, vp, sz, C.POINTER(u64)]),
+        "b200msm_table_shape": (C.c_bool, [u64, C.POINTER(sz), C.POINTER(sz), C.POINTER(sz),
+                                           C.POINTER(sz)]),
+        "b200msm_table_download": (C.c_bool, [u64, C.POINTER(vp), sz, sz]),
+        "b200msm_batch_exp_resident": (C.c_bool, [u32, u64, vp, sz, sz, vp, sz, vp, sz]),
+        "b200msm_device_timings": (sz, [sz, C.POINTER(C.c_float), sz]),
     }
     for name, (res, args) in sigs.items():
         f = getattr(L, name)
@@ -138,6 +157,32 @@ def init(device: Optional[int] = None) -> int:
         _fail("b200msm_init")
     _bound_device = int(device)
     return _bound_device
+
+
+def init_devices(devices: Sequence[int]) -> int:
+    """Binds several GPUs of the box (b200msm_init_devices): every later multi_exp / batch call
+    cuts its range into one contiguous range per device, as the reference cuts it into `chunks`
+    (multiexp.tcc:655-687).  A device may be listed twice (two contexts on one GPU; a test aid)."""
+    global _bound_device
+    ids = (C.c_int * len(devices))(*[int(d) for d in devices])
+    if not load().b200msm_init_devices(ids, len(devices)):
+        _fail("b200msm_init_devices")
+    _bound_device = int(devices[0])
+    return len(devices)
+
+
+def init_all() -> int:
+    """Binds every visible CUDA device; returns their number."""
+    global _bound_device
+    k = int(load().b200msm_init_all())
+    if k <= 0:
+        _fail("b200msm_init_all")
+    _bound_device = 0
+    return k
+
+
+def device_count() -> int:
+    return int(load().b200msm_device_count())
 
 
 def shutdown() -> None:
@@ -222,18 +267,20 @@ def multi_exp_host_ptr(group: int, bases_ptr: int, scalars_ptr: int, n: int,
     return out
 
 
-WIRE_CHECK_CURVE, WIRE_CHECK_SUBGROUP = 1, 2
+# opt-outs of the point checks group_element_read always makes (ffi_serialization.tcc:165)
+WIRE_SKIP_CURVE_CHECK, WIRE_SKIP_SUBGROUP_CHECK = 1, 2
 
 
 def wire_point_bytes(group: int) -> int:
     return int(load().b200msm_wire_point_bytes(group))
 
 
-def multi_exp_wire(group: int, points: bytes, scalars: bytes, flags: int = WIRE_CHECK_CURVE) -> bytes:
+def multi_exp_wire(group: int, points: bytes, scalars: bytes, flags: int = 0) -> bytes:
     """MSM on the byte format of the reference's ffi layer (ffi/ffi_serialization.hpp:12-16): affine
     big-endian plain X | Y points ((0, 1) = infinity) and big-endian plain scalars; returns the
-    affine result in the same format.  Raises on malformed input, as the reference's readers
-    return false (ffi_serialization.tcc:64-75,165)."""
+    affine result in the same format.  Raises on malformed input -- a value >= its modulus, a point
+    off the curve or outside the prime-order subgroup -- as the reference's readers return false
+    (ffi_serialization.tcc:64-75,165); `flags` opts out of a point check."""
     _ensure_init()
     pb, sb = wire_point_bytes(group), scalar_bytes(group)
     if pb == 0:
@@ -298,20 +345,37 @@ def debug_op(group: int, op: int, a, b=None) -> np.ndarray:
     return out
 
 
-def batch_exp(group: int, scalar_size: int, window: int, table: Sequence, scalars) -> np.ndarray:
+def batch_exp(group: int, scalar_size: int, window: int, table, scalars) -> np.ndarray:
     """libff::batch_exp<G, Fr>(scalar_size, window, table, v).  `table` is a sequence of rows
-    (window_table<G> = vector<vector<G>>) or a (rows, 1 << window, words) array."""
+    (window_table<G> = vector<vector<G>>), a (rows, 1 << window, words) array, or a resident
+    WindowTable."""
+    return batch_exp_with_coeff(group, scalar_size, window, table, None, scalars)
+
+
+def batch_exp_with_coeff(group: int, scalar_size: int, window: int, table, coeff,
+                         scalars) -> np.ndarray:
+    """libff::batch_exp_with_coeff<G, Fr>(scalar_size, window, table, coeff, v) (multiexp.tcc:
+    917-947): out[i] = (coeff * v[i]) g.  coeff: one Fr element (Montgomery limbs) or None."""
     _ensure_init()
     gb, sb = group_bytes(group), scalar_bytes(group)
-    rows = [_as_u64(r, "table row") for r in table]
     s = _as_u64(scalars, "scalars")
     n = _count(s, sb, "scalars")
+    out = np.zeros((n, gb // 8), dtype=np.uint64)
+    cf = None if coeff is None else _as_u64(coeff, "coeff").reshape(-1)
+    cp, cb = (None, 0) if cf is None else (_ptr(cf), cf.nbytes)
+    if isinstance(table, WindowTable):
+        if (table.scalar_size, table.window) != (scalar_size, window):
+            raise B200MsmError("batch_exp: the resident table was built for another shape")
+        if not load().b200msm_batch_exp_resident(group, table.handle, _ptr(s), s.nbytes, n, cp, cb,
+                                                 _ptr(out), out.nbytes):
+            _fail("b200msm_batch_exp_resident")
+        return out
+    rows = [_as_u64(r, "table row") for r in table]
     row_len = _count(rows[0], gb, "table row") if rows else 0
     ptrs = (C.c_void_p * len(rows))(*[r.ctypes.data for r in rows])
-    out = np.zeros((n, gb // 8), dtype=np.uint64)
-    if not load().b200msm_batch_exp(group, scalar_size, window, ptrs, len(rows), row_len, _ptr(s),
-                                    s.nbytes, n, _ptr(out), out.nbytes):
-        _fail("b200msm_batch_exp")
+    if not load().b200msm_batch_exp_with_coeff(group, scalar_size, window, ptrs, len(rows), row_len,
+                                               cp, cb, _ptr(s), s.nbytes, n, _ptr(out), out.nbytes):
+        _fail("b200msm_batch_exp_with_coeff")
     return out
 
 
@@ -329,6 +393,40 @@ class _Resident:
             self.release()
         except Exception:
             pass
+
+
+class WindowTable(_Resident):
+    """A fixed-base window table kept in HBM, normalised once (get_window_table, multiexp.tcc:
+    809-846).  `g=`: built on the device from the base; `table=`: uploaded from host rows."""
+
+    def __init__(self, group: int, scalar_size: int, window: int, g=None, table=None):
+        _ensure_init()
+        h = C.c_uint64(0)
+        gb = group_bytes(group)
+        self.scalar_size, self.window = scalar_size, window
+        self.rows = (scalar_size + window - 1) // window
+        if g is not None:
+            ga = _as_u64(g, "g").reshape(-1)
+            if not load().b200msm_table_build(group, scalar_size, window, _ptr(ga), ga.nbytes,
+                                              C.byref(h)):
+                _fail("b200msm_table_build")
+        else:
+            rows = [_as_u64(r, "table row") for r in table]
+            row_len = _count(rows[0], gb, "table row") if rows else 0
+            ptrs = (C.c_void_p * len(rows))(*[r.ctypes.data for r in rows])
+            if not load().b200msm_table_upload(group, scalar_size, window, ptrs, len(rows), row_len,
+                                               C.byref(h)):
+                _fail("b200msm_table_upload")
+        super().__init__(h.value, group, self.rows << window)
+
+    def download(self) -> np.ndarray:
+        """(rows, 1 << window, words) array in the reference's layout, special form."""
+        words = group_bytes(self.group) // 8
+        out = np.zeros((self.rows, 1 << self.window, words), dtype=np.uint64)
+        ptrs = (C.c_void_p * self.rows)(*[out[r].ctypes.data for r in range(self.rows)])
+        if not load().b200msm_table_download(self.handle, ptrs, self.rows, 1 << self.window):
+            _fail("b200msm_table_download")
+        return out
 
 
 class ResidentBases(_Resident):
@@ -364,6 +462,28 @@ def multi_exp_resident(bases: ResidentBases, scalars: ResidentScalars, first: in
     if not load().b200msm_multi_exp_resident(group, bases.handle, scalars.handle, first, n,
                                              _ptr(out), out.nbytes):
         _fail("b200msm_multi_exp_resident")
+    return out
+
+
+def multi_exp_resident_bases(bases: ResidentBases, scalars) -> np.ndarray:
+    """The prover-shaped call: resident bases, host scalars uploaded under the computation."""
+    group = bases.group
+    s = _as_u64(scalars, "scalars")
+    n = _count(s, scalar_bytes(group), "scalars")
+    out = np.zeros(group_bytes(group) // 8, dtype=np.uint64)
+    if not load().b200msm_multi_exp_resident_bases(group, bases.handle, _ptr(s), s.nbytes, n,
+                                                   _ptr(out), out.nbytes):
+        _fail("b200msm_multi_exp_resident_bases")
+    return out
+
+
+def multi_exp_resident_bases_ptr(bases: ResidentBases, scalars_ptr: int, n: int) -> np.ndarray:
+    """multi_exp_resident_bases on a raw host address (e.g. a pinned buffer owned by the caller)."""
+    group = bases.group
+    out = np.zeros(group_bytes(group) // 8, dtype=np.uint64)
+    if not load().b200msm_multi_exp_resident_bases(group, bases.handle, C.c_void_p(scalars_ptr),
+                                                   n * scalar_bytes(group), n, _ptr(out), out.nbytes):
+        _fail("b200msm_multi_exp_resident_bases")
     return out
 
 
@@ -424,6 +544,8 @@ def multi_exp_precomputed(table: PrecomputedBases, scalars) -> np.ndarray:
 
 # ---- streamed bases (multi_exp_stream, multiexp_stream.tcc:164-193) ------------------------------
 STREAM_MEMORY_SPECIAL, STREAM_MEMORY_NORMAL, STREAM_BINARY_PLAIN, STREAM_BINARY_MONTGOMERY = 0, 1, 2, 3
+# or'ed into precompute_c: reproduce the reference's dropped top carry (field_utils.tcc:205-239)
+STREAM_REFERENCE_CARRY = 0x100
 
 
 class MsmStream:
@@ -432,14 +554,15 @@ class MsmStream:
     encoding (decoded on the device).  precompute_c != 0: every base comes as its multiples."""
 
     def __init__(self, group: int, scalars, encoding: int = STREAM_MEMORY_SPECIAL,
-                 precompute_c: int = 0):
+                 precompute_c: int = 0, reference_carry: bool = False):
         _ensure_init()
         s = _as_u64(scalars, "scalars")
         self.group, self.n = group, _count(s, scalar_bytes(group), "scalars")
         self.encoding, self.c = encoding, precompute_c
         h = C.c_uint64(0)
-        if not load().b200msm_stream_begin(group, _ptr(s), s.nbytes, self.n, encoding, precompute_c,
-                                           C.byref(h)):
+        flag = STREAM_REFERENCE_CARRY if (reference_carry and precompute_c) else 0
+        if not load().b200msm_stream_begin(group, _ptr(s), s.nbytes, self.n, encoding,
+                                           precompute_c | flag, C.byref(h)):
             _fail("b200msm_stream_begin")
         self.handle = h.value
 
@@ -477,6 +600,14 @@ def last_timings() -> dict:
     L = load()
     buf = (C.c_float * 16)()
     k = L.b200msm_last_timings(buf, 16)
+    return {L.b200msm_timing_name(i).decode(): float(buf[i]) for i in range(k)}
+
+
+def device_timings(index: int) -> dict:
+    """phase timings of one bound device (last_timings is the maximum over the devices)"""
+    L = load()
+    buf = (C.c_float * 16)()
+    k = L.b200msm_device_timings(index, buf, 16)
     return {L.b200msm_timing_name(i).decode(): float(buf[i]) for i in range(k)}
 
 

@@ -116,34 +116,110 @@ __global__ void k_apply_zinv(const uint32_t *raw, const uint32_t *__restrict__ z
 }
 
 // windowed_exp (multiexp.tcc:848-873): out[i] = sum_r table[r][bits(s_i, r*w, w)], table already
-// normalised to device affine, row-major rows x row_len.
+// normalised to device affine, row-major rows x row_len.  With `coeff` the exponent is
+// coeff * v[i] (batch_exp_with_coeff, multiexp.tcc:917-947: one Fr product ahead of the digits).
 template <class C>
 __global__ void __launch_bounds__(128)
-    k_batch_exp(const uint32_t *__restrict__ scalars, const uint32_t *__restrict__ table_aff,
-                uint32_t rows, uint32_t row_len, int window, uint32_t *__restrict__ out_raw,
-                uint32_t n) {
+    k_batch_exp(const uint32_t *__restrict__ scalars, const uint32_t *__restrict__ coeff,
+                const uint32_t *__restrict__ table_aff, uint32_t rows, uint32_t row_len, int window,
+                uint32_t *__restrict__ out_raw, uint32_t n) {
     using R = Raw<C>;
     using F = typename C::Fq;
     using Fr = typename C::Fr;
     using X = XYZZ<F>;
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    Fr s = Fr::from_mont(Fr::load(scalars + (size_t)i * Fr::N));
+    Fr s = Fr::load(scalars + (size_t)i * Fr::N);
+    if (coeff != nullptr) s = Fr::mul(Fr::load(coeff), s);  // Montgomery forms: stays one
+    s = Fr::from_mont(s);
     const uint32_t mask = (1u << window) - 1;
     X acc = X::inf();
+    // the next row's entry is fetched while the current addition runs
+    uint32_t d = s.v[0] & mask;
+    Affine<F> p = Affine<F>::load(table_aff + (size_t)(d < row_len ? d : 0) * R::AW);
     for (uint32_t r = 0; r < rows; r++) {
-        uint32_t d = s.v[0] & mask;
+        const Affine<F> pcur = p;
 #pragma unroll
         for (int k = 0; k < Fr::N - 1; k++) s.v[k] = __funnelshift_r(s.v[k], s.v[k + 1], window);
         s.v[Fr::N - 1] >>= window;
-        if (d < row_len) {
-            Affine<F> p = Affine<F>::load(table_aff + ((size_t)r * row_len + d) * R::AW);
-            if (!p.is_inf()) X::madd(acc, p.x, p.y);
+        if (r + 1 < rows) {
+            d = s.v[0] & mask;
+            p = Affine<F>::load(table_aff + ((size_t)(r + 1) * row_len + (d < row_len ? d : 0)) * R::AW);
         }
+        if (!pcur.is_inf()) X::madd(acc, pcur.x, pcur.y);
     }
     F Xo, Yo, Zo;
     R::from_xyzz(acc, Xo, Yo, Zo);
     R::store(out_raw + (size_t)i * R::PW, Xo, Yo, Zo);
+}
+
+// the same point over the same field with another inline / call policy (identical word layout)
+template <class XB, class XA>
+B200_DEV XB xyzz_cast(const XA &p) {
+    uint32_t tmp[XA::WORDS];
+    p.store(tmp);
+    return XB::load(tmp);
+}
+
+// ---- get_window_table on the device (multiexp.tcc:809-846) --------------------------------------
+// row_base[r] = 2^(r w) g: thread r walks its own r w doublings (the longest chain, scalar_bits
+// doublings, is what the reference's serial loop walks too, :838-840).
+template <class C>
+__global__ void k_table_row_bases(const uint32_t *__restrict__ g_raw, int window, uint32_t rows,
+                                  uint32_t *__restrict__ row_base) {
+    using R = Raw<C>;
+    using F = typename C::Fq;
+    using X = XYZZ<TailField<F>>;
+    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= rows) return;
+    F Xi, Yi, Zi;
+    R::load(g_raw, Xi, Yi, Zi);
+    X p = xyzz_cast<X>(R::to_xyzz(Xi, Yi, Zi));
+    for (uint32_t k = 0; k < r * (uint32_t)window; k++) p = X::dbl(p);
+    p.store(row_base + (size_t)r * R::XW);
+}
+
+// entries [r][j0 .. j0 + TABLE_RUN): the first by double-and-add (j0 * row_base[r]), the rest by
+// running additions of row_base[r] -- the reference's inner loop (:830-833) cut into runs.
+constexpr uint32_t TABLE_RUN = 64;
+template <class C>
+__global__ void __launch_bounds__(64)
+    k_table_fill(const uint32_t *__restrict__ row_base, uint32_t rows, uint32_t row_len,
+                 uint32_t last_len, uint32_t *__restrict__ table_raw) {
+    using R = Raw<C>;
+    using F = TailField<typename C::Fq>;
+    using X = XYZZ<F>;
+    const uint32_t runs = (row_len + TABLE_RUN - 1) / TABLE_RUN;
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= rows * runs) return;
+    const uint32_t r = t / runs, j0 = (t % runs) * TABLE_RUN;
+    const uint32_t len = r + 1 == rows ? last_len : row_len;  // filled entries of this row
+    const X base = X::load(row_base + (size_t)r * R::XW);
+    X cur = small_mul<F>(base, j0);
+    for (uint32_t j = j0; j < j0 + TABLE_RUN && j < row_len; j++) {
+        uint32_t *dst = table_raw + ((size_t)r * row_len + j) * R::PW;
+        typename C::Fq Xo, Yo, Zo;
+        if (j < len) {
+            R::from_xyzz(xyzz_cast<XYZZ<typename C::Fq>>(cur), Xo, Yo, Zo);
+            X::add(cur, base);
+        } else {  // T::zero() tail of the last row
+            Xo = C::Fq::zero(), Yo = C::Fq::one(), Zo = C::Fq::zero();
+        }
+        R::store(dst, Xo, Yo, Zo);
+    }
+}
+
+// device affine ((0, 0) = zero) -> the reference's special form (x, y, 1) / (0, 1, 0)
+template <class C>
+__global__ void k_affine_to_special(const uint32_t *__restrict__ aff, uint32_t *__restrict__ raw,
+                                    uint32_t n) {
+    using R = Raw<C>;
+    using F = typename C::Fq;
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const Affine<F> p = Affine<F>::load(aff + (size_t)i * R::AW);
+    const bool inf = p.is_inf();
+    R::store(raw + (size_t)i * R::PW, p.x, inf ? F::one() : p.y, inf ? F::zero() : F::one());
 }
 
 }  // namespace b200msm

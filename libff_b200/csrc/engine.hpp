@@ -77,13 +77,39 @@ enum Slot {
     SL_PRE_RAW,     // the same in reference layout, input of the batch normalisation
     SL_STREAM_IN,   // encoded chunk of a streamed MSM
     SL_LIVE,        // per bucket: written by an earlier point range of the same call
+    SL_SUM_IN,      // partial points of the device shards, summed on the first device
+    SL_DIGITS_B,    // second digit / rank set: the sort of one window group under the
+    SL_RANKS_B,     //   accumulation of the previous one
+    SL_SORTED_B,
+    SL_SEG_BUCKET_B,
+    SL_OFFSETS_B,
+    SL_META,        // item count of a sort, highest window in use
     SL_COUNT
 };
 
 constexpr int MAX_H2D_PARTS = 16;
 
+// Pinned staging ring of one engine context.  Pageable sources -- what a std::vector<G> of a libff
+// caller is -- would be staged by the driver at ~10 GB/s; instead STAGE_LANES host threads copy
+// slices into these buffers and issue the DMA from there, which keeps the PCIe link busy.
+constexpr int STAGE_LANES = 4;
+constexpr size_t STAGE_BYTES = (size_t)8 << 20;
+struct Stager {
+    void *buf[STAGE_LANES][2] = {};
+    cudaEvent_t ev[STAGE_LANES][2] = {};
+    bool ready = false;
+    bool init();
+    void release();
+};
+
+// One engine context per bound device (b200msm_init_devices): its streams, events, scratch pool
+// and options.  Nothing in the pipelines is process-global, so several contexts -- one per GPU of
+// the box -- run concurrently from their own host threads.
 struct Ctx {
     int device = -1;
+    int index = 0;               // position in the list of bound devices
+    uint32_t attr_mask = 0;      // groups whose kernels have had their function attributes set
+    Stager stager;
     cudaStream_t stream = nullptr;
     cudaStream_t copy_stream = nullptr;          // host -> device uploads of a pipelined call
     cudaEvent_t ev_copy[MAX_H2D_PARTS] = {};     // "range k is on the device"
@@ -97,6 +123,12 @@ struct Ctx {
     // `acc_stream`, the reductions that follow each of them go to `tail_stream`
     cudaStream_t acc_stream = nullptr;
     cudaEvent_t ev_group_go = nullptr, ev_group[2] = {};
+    // the counting sort of window group g + 1 (L2 / atomic bound) runs here under the
+    // accumulation of group g (multiply-pipe bound)
+    cudaStream_t sort_stream = nullptr;
+    cudaEvent_t ev_sort[4] = {};  // [p]: sort into buffer set p done; [2 + p]: its reader done
+    int sort_parity = 0;          // buffer set the next sort writes
+    bool sort_inputs_ready = false;  // the caller queued the inputs' upload / ingest on sort_stream
     bool defer_tail = false;    // set by the pipelined caller
     // Point ranges of ONE host-buffer call that share a bucket set (set by the pipelined caller):
     // every range runs digits / sort / accumulation with the digit size of the whole call and adds
@@ -120,6 +152,9 @@ struct Ctx {
     int opt_window_groups = 0; // groups the windows are walked in (top-down); 0 = automatic, 1 = one
     int opt_carry_segment = 0; // carries per thread in the later accumulation rounds; 0 = automatic
     int opt_reduce_chunk = 0; // log2 of the buckets per thread in the reduction; 0 = automatic
+    int opt_h2d_pack = 1;     // special-form bases leave Z behind on upload: 0 never, 1 pageable sources, 2 always
+    int opt_sort_overlap = 0; // window groups whose sort overlaps the previous accumulation; 0 = automatic
+    int opt_coop_accum = 0;   // lane-cooperative accumulation of the wide fields: 0 automatic, 1 off, 2 on
 
     bool reserve(Slot s, size_t bytes, void **out);
     void release_all();
@@ -141,6 +176,10 @@ struct MsmShape {
     int W;              // digits per scalar = multiples per base = ceil(scalar bits / c)
     uint32_t pstride;   // table index stride between bases
     uint32_t wstride;   // table index stride between multiples of one base
+    // Where W c equals the scalar width the reference's field_get_signed_digits drops the carry out
+    // of the top digit (field_utils.tcc:205-239).  false: such scalars are folded to r - s and the
+    // result is the true sum; true: the carry is dropped as the reference does, bit for bit.
+    bool drop_top_carry = false;
 };
 
 // Type-erased per-group entry points, implemented once per group in group_*.cu.
@@ -148,22 +187,35 @@ struct GroupOps {
     uint32_t id;
     size_t group_bytes, scalar_bytes, affine_bytes;
     int scalar_bits;
-    // d_raw (reference layout, device) -> d_aff, d_inf
+    // d_raw (reference layout, device) -> d_aff, d_inf.  form 0: any Z, 1: special (Z = 1 or the
+    // zero element), 2: d_raw == d_aff already holds device-affine records (packed upload): flags only
     bool (*ingest)(Ctx &, const void *d_raw, size_t n, uint32_t form, void *d_aff, uint8_t *d_inf);
-    // the MSM proper; result (reference layout) into d_out
+    // the MSM proper; result (reference layout) into d_out.  With a shape, d_inf holds one flag
+    // per table ENTRY (index i * pstride + w * wstride), else one per base.
     bool (*msm)(Ctx &, const void *d_aff, const uint8_t *d_inf, const void *d_scalars, size_t n,
                 void *d_out, const MsmShape *shape);
-    // table[w * n + i] = 2^(w c) P_i (device affine), w < W, from n device-affine bases
+    // reserves the scratch of an MSM over n points (upper bounds), so that a pipelined call does
+    // not regrow slots between its ranges
+    bool (*msm_prepare)(Ctx &, size_t n, const MsmShape *shape);
+    // table[w * n + i] = 2^(w c) P_i (device affine), w < W, from n device-affine bases;
+    // d_table_inf[w * n + i] = 1 where that multiple is the zero element
     bool (*precompute)(Ctx &, const void *d_aff, const uint8_t *d_inf, size_t n, int c, int W,
-                       void *d_table);
+                       void *d_table, uint8_t *d_table_inf);
     // libff's binary stream encoding (curve_serialization.tcc:79-101, uncompressed) -> device
     // affine + infinity flags; flags bit 0: Montgomery form (else plain)
     bool (*stream_decode)(Ctx &, const void *d_bytes, size_t n, uint32_t flags, void *d_aff,
                           uint8_t *d_inf);
     bool (*sum)(Ctx &, const void *d_raw, size_t count, void *d_out);
     bool (*to_special)(Ctx &, void *d_raw, size_t n);
-    bool (*batch_exp)(Ctx &, const void *d_table_raw, size_t rows, size_t row_len, int window,
-                      const void *d_scalars, size_t n, void *d_out);
+    // fixed-base tables (multiexp.tcc:809-846): raw reference-layout entries -> device affine
+    // ((0, 0) = zero element); the device build of get_window_table; affine -> special-form raw
+    bool (*table_normalise)(Ctx &, const void *d_table_raw, size_t entries, void *d_table_aff);
+    bool (*table_build)(Ctx &, const void *d_g_raw, int scalar_bits, int window, size_t rows,
+                        size_t row_len, void *d_table_raw);
+    bool (*table_export)(Ctx &, const void *d_table_aff, size_t entries, void *d_table_raw);
+    // out[i] = windowed_exp(table, [coeff *] scalars[i]) (multiexp.tcc:848-947); d_coeff may be null
+    bool (*batch_exp)(Ctx &, const void *d_table_aff, size_t rows, size_t row_len, int window,
+                      const void *d_scalars, const void *d_coeff, size_t n, void *d_out);
     uint32_t (*window_bits)(const Ctx &, size_t n);
     // wire format of the reference's ffi layer (wire_kernels.cuh): decode + validate, encode
     bool (*wire_decode)(Ctx &, const void *d_wire_points, const void *d_wire_scalars, size_t n,

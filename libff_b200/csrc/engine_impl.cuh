@@ -113,6 +113,12 @@ bool to_special_impl(Ctx &ctx, void *d_raw, size_t n) {
 template <class C>
 bool ingest_impl(Ctx &ctx, const void *d_raw, size_t n, uint32_t form, void *d_aff, uint8_t *d_inf) {
     if (n == 0) return true;
+    if (form == 2) {  // packed upload: d_raw == d_aff holds device-affine records already
+        k_flags_from_affine<C><<<cdiv(n, 256), 256, 0, ctx.stream>>>((const uint32_t *)d_aff, d_inf,
+                                                                   (uint32_t)n);
+        B200_LAUNCH_CHECK(ctx);
+        return true;
+    }
     if (form == 1) {
         k_ingest_special<C><<<cdiv(n, 128), 128, 0, ctx.stream>>>((const uint32_t *)d_raw,
                                                                 (uint32_t *)d_aff, d_inf, (uint32_t)n);
@@ -159,11 +165,140 @@ inline uint32_t pick_segment(const Ctx &ctx, size_t total) {
     return seg;
 }
 
+// ------------------------------------------------------------------------------------------
+// Geometry of one MSM call
+template <class C>
+struct MsmGeom {
+    bool pre, ranged;
+    int c, W;
+    uint32_t B, bstride;
+    size_t M;
+    int fold_bit;
+};
+
+template <class C>
+MsmGeom<C> msm_geom(const Ctx &ctx, size_t n, const MsmShape *shape) {
+    MsmGeom<C> g;
+    g.pre = shape != nullptr;
+    // shared-bucket point ranges of one call (Ctx::range_c): fixed digit size, buckets kept
+    g.ranged = !g.pre && ctx.range_c > 0;
+    g.c = g.pre ? shape->c : g.ranged ? ctx.range_c : (int)pick_window_bits<C>(ctx, n);
+    g.W = g.pre ? shape->W : (C::Fr::Params::BITS + 1 + g.c - 1) / g.c;
+    g.B = 1u << (g.c - 1);
+    g.bstride = g.pre ? 0u : g.B;  // precomputed multiples share one bucket set
+    g.M = g.pre ? (size_t)g.B : (size_t)g.W * g.B;
+    // W c == scalar bits: the top digit may carry out.  Default: k_digits folds such scalars to
+    // r - s (the true sum); drop_top_carry: the reference's recoding, carry dropped (-2).
+    g.fold_bit = -1;
+    if (g.pre && g.W * g.c - 1 < C::Fr::Params::BITS) g.fold_bit = g.W * g.c - 1;
+    if (g.pre && shape->drop_top_carry) g.fold_bit = -2;
+    return g;
+}
+
+// Groups of windows (ascending).  The counting sort of group g + 1 -- digit pass, scan, scatter:
+// L2-atomic / random-access bound -- runs on the sort stream under the accumulation of group g,
+// which is bound by the integer multiply pipe: different resources, so the 10 % of the step the
+// sort used to hold at 2^24 disappears behind the accumulation.  The first group is one window,
+// so that the only exposed sort is short.
+inline std::vector<int> pick_sort_groups(const Ctx &ctx, size_t n, int W, bool single) {
+    std::vector<int> sizes;
+    int want = ctx.opt_sort_overlap ? ctx.opt_sort_overlap : ctx.opt_window_groups;
+    if (single || W <= 2 || want == 1) return {W};
+    if (want == 0) {
+        if ((uint64_t)n * W < (1ull << 23)) return {W};  // small inputs: launch overheads dominate
+        want = (W + 2) / 3 + 1;
+    }
+    want = std::min(want, W);
+    sizes.push_back(1);
+    int left = W - 1;
+    for (int g = 1; g < want; g++) {
+        const int take = (left + (want - g) - 1) / (want - g);
+        sizes.push_back(take);
+        left -= take;
+    }
+    return sizes;
+}
+
+// Upper bound of the accumulation threads (= carry entries) of a group holding `items` sorted items
+template <class C>
+inline size_t segments_bound(const Ctx &ctx, size_t items) {
+    if (ctx.opt_segment > 0) return items / (((size_t)ctx.opt_segment + 3u) & ~(size_t)3u) + 2;
+    constexpr bool ext = BaseLimbs<typename C::Fq>::EXT;
+    constexpr int limbs = BaseLimbs<typename C::Fq>::N;
+    const size_t want_threads = (!ext && limbs >= 24) ? 148 * 128 : 148 * 384 * 4;
+    return std::max<size_t>(2 * want_threads, items / (ext ? 64 : 128)) + 2;
+}
+
+// Scratch of one MSM, reserved once before any kernel is queued (nothing regrows mid-call)
+template <class C>
+struct MsmScratch {
+    int32_t *digits[2];
+    uint32_t *ranks[2], *seg_bucket[2], *offsets[2];
+    Entry *sorted[2];
+    uint32_t *hist, *buckets, *meta, *tile_sums, *live;
+    uint32_t *keyA, *ptA, *keyB, *ptB, *keyC, *ptC;
+    size_t carry_cap;
+};
+
+template <class C>
+bool msm_reserve(Ctx &ctx, const MsmGeom<C> &g, size_t n, const std::vector<int> &groups,
+                 MsmScratch<C> &sc) {
+    using R = Raw<C>;
+    int wg_max = 0;
+    for (int w : groups) wg_max = std::max(wg_max, w);
+    const size_t items = (size_t)wg_max * n;
+    const bool two = groups.size() > 1 || g.ranged;  // a second buffer set only where sorts overlap
+    static const Slot DIG[2] = {SL_DIGITS, SL_DIGITS_B}, RNK[2] = {SL_RANKS, SL_RANKS_B},
+                      SRT[2] = {SL_SORTED, SL_SORTED_B}, SGB[2] = {SL_SEG_BUCKET, SL_SEG_BUCKET_B},
+                      OFF[2] = {SL_OFFSETS, SL_OFFSETS_B};
+    size_t carry_cap = 0;
+    for (int w : groups) carry_cap += segments_bound<C>(ctx, (size_t)w * n);
+    for (int b = 0; b < 2; b++) {
+        if (b == 1 && !two) {
+            sc.digits[1] = sc.digits[0], sc.ranks[1] = sc.ranks[0], sc.sorted[1] = sc.sorted[0];
+            sc.seg_bucket[1] = sc.seg_bucket[0], sc.offsets[1] = sc.offsets[0];
+            break;
+        }
+        if (!reserve_as(ctx, DIG[b], items * 4, &sc.digits[b])) return false;
+        if (!reserve_as(ctx, RNK[b], items * 4, &sc.ranks[b])) return false;
+        // the sorted array is read four items at a time
+        if (!reserve_as(ctx, SRT[b], (items + 4) * sizeof(Entry), &sc.sorted[b])) return false;
+        if (!reserve_as(ctx, SGB[b], (segments_bound<C>(ctx, items) + 1) * 4, &sc.seg_bucket[b]))
+            return false;
+        // every group's slice is followed by one extra entry (its item count)
+        if (!reserve_as(ctx, OFF[b], (g.M + groups.size() + 2) * 4, &sc.offsets[b])) return false;
+    }
+    if (!reserve_as(ctx, SL_HIST, g.M * 4, &sc.hist)) return false;
+    if (!reserve_as(ctx, SL_BUCKETS, g.M * R::XW * 4, &sc.buckets)) return false;
+    if (!reserve_as(ctx, SL_META, 64, &sc.meta)) return false;
+    const size_t tiles_max = (size_t)cdiv(g.M, SCAN_TILE) + 1;
+    if (!reserve_as(ctx, SL_TILE_SUMS, (tiles_max + 1) * 4, &sc.tile_sums)) return false;
+    sc.live = nullptr;
+    if (g.ranged && !reserve_as(ctx, SL_LIVE, g.M * 4, &sc.live)) return false;
+    const uint32_t SEG_CARRY = pick_carry_segment<C>(ctx);
+    const size_t t2 = (carry_cap + 1 + SEG_CARRY - 1) / SEG_CARRY, t3 = (t2 + SEG_CARRY - 1) / SEG_CARRY;
+    if (!reserve_as(ctx, SL_CARRY_KEY_A, carry_cap * 4, &sc.keyA)) return false;
+    if (!reserve_as(ctx, SL_CARRY_PT_A, carry_cap * R::XW * 4, &sc.ptA)) return false;
+    if (!reserve_as(ctx, SL_CARRY_KEY_B, t2 * 4, &sc.keyB)) return false;
+    if (!reserve_as(ctx, SL_CARRY_PT_B, t2 * R::XW * 4, &sc.ptB)) return false;
+    if (!reserve_as(ctx, SL_CARRY_KEY_C, t3 * 4, &sc.keyC)) return false;
+    if (!reserve_as(ctx, SL_CARRY_PT_C, t3 * R::XW * 4, &sc.ptC)) return false;
+    sc.carry_cap = carry_cap;
+    return true;
+}
+
+template <class C>
+bool msm_prepare_impl(Ctx &ctx, size_t n, const MsmShape *shape) {
+    if (n == 0) return true;
+    const MsmGeom<C> g = msm_geom<C>(ctx, n, shape);
+    MsmScratch<C> sc;
+    return msm_reserve<C>(ctx, g, n, pick_sort_groups(ctx, n, g.W, g.pre || g.ranged), sc);
+}
+
 template <class C>
 bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_scalars, size_t n,
               void *d_out, const MsmShape *shape) {
     using R = Raw<C>;
-    using F = typename C::Fq;
     cudaStream_t st = ctx.stream;
     if (n == 0) {  // multiexp.tcc:291-309: zero element
         k_sum_raw<C><<<1, 32, 0, st>>>(nullptr, 0, (uint32_t *)d_out);
@@ -174,88 +309,26 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
         set_error("multi_exp: n = %zu exceeds the 2^31 - 1 points one device shard addresses", n);
         return false;
     }
-    const bool pre = shape != nullptr;
-    // shared-bucket point ranges of one call (Ctx::range_c): fixed digit size, buckets kept
-    const bool ranged = !pre && ctx.range_c > 0;
+    const MsmGeom<C> geo = msm_geom<C>(ctx, n, shape);
+    const bool pre = geo.pre, ranged = geo.ranged;
     const bool range_first = !ranged || ctx.range_first, range_last = !ranged || ctx.range_last;
-    const int c = pre ? shape->c : ranged ? ctx.range_c : (int)pick_window_bits<C>(ctx, n);
-    const int W = pre ? shape->W : (C::Fr::Params::BITS + 1 + c - 1) / c;
-    const uint32_t B = 1u << (c - 1);
-    const uint32_t bstride = pre ? 0u : B;         // precomputed multiples share one bucket set
-    const size_t M = pre ? (size_t)B : (size_t)W * B;
-    // W c == scalar bits: the top digit may carry out; k_digits folds such scalars to r - s
-    const int fold_bit = pre && W * c - 1 < C::Fr::Params::BITS ? W * c - 1 : -1;
+    const int c = geo.c, W = geo.W;
+    const uint32_t B = geo.B, bstride = geo.bstride;
+    const size_t M = geo.M;
     if ((uint64_t)n * W >= (pre ? (1ull << 31) : (1ull << 32))) {
         set_error("multi_exp: n * windows = %llu does not fit 32-bit positions",
                   (unsigned long long)n * W);
         return false;
     }
-    int32_t *digits;
-    uint32_t *hist, *offsets, *buckets, *chunks, *windows;
-    Entry *sorted;
-    if (!reserve_as(ctx, SL_DIGITS, (size_t)W * n * 4, &digits)) return false;
-    if (!reserve_as(ctx, SL_HIST, M * 4, &hist)) return false;
-    if (!reserve_as(ctx, SL_OFFSETS, (M + 2) * 4, &offsets)) return false;  // + total, used windows
-    if (!reserve_as(ctx, SL_BUCKETS, M * R::XW * 4, &buckets)) return false;
+    std::vector<int> gsizes = pick_sort_groups(ctx, n, W, pre || ranged);
+    MsmScratch<C> sc;
+    if (!msm_reserve<C>(ctx, geo, n, gsizes, sc)) return false;
+    uint32_t *const buckets = sc.buckets;
+    uint32_t *const used_windows = sc.meta + 8;
 
-    // --- digits + histogram
-    B200_CUDA(cudaMemsetAsync(hist, 0, M * 4, st));
-    // (the highest used window is a maximum over all ranges of a call)
-    if (range_first) B200_CUDA(cudaMemsetAsync(offsets + M + 1, 0, 4, st));
-    uint32_t *live = nullptr;
-    if (ranged) {
-        if (!reserve_as(ctx, SL_LIVE, M * 4, &live)) return false;
-        if (range_first) B200_CUDA(cudaMemsetAsync(live, 0, M * 4, st));
-    }
-    uint32_t *ranks;
-    if (!reserve_as(ctx, SL_RANKS, (size_t)W * n * 4, &ranks)) return false;
-    k_digits<C><<<cdiv(n, 256), 256, 0, st>>>((const uint32_t *)d_scalars, d_inf, digits, ranks, hist,
-                                               offsets + M + 1, (uint32_t)n, c, W, bstride, fold_bit);
-    B200_LAUNCH_CHECK(ctx);
-    B200_CUDA(cudaEventRecord(ctx.ev[PH_DIGITS + 1], st));
-    // --- offsets
-    const uint32_t tiles = cdiv(M, SCAN_TILE);
-    uint32_t *tile_sums;
-    if (!reserve_as(ctx, SL_TILE_SUMS, ((size_t)tiles + 1) * 4, &tile_sums)) return false;
-    k_scan_tiles<<<tiles, SCAN_THREADS, 0, st>>>(hist, tile_sums, (uint32_t)M);
-    B200_LAUNCH_CHECK(ctx);
-    k_scan_tile_sums<<<1, 1024, 0, st>>>(tile_sums, tiles);
-    B200_LAUNCH_CHECK(ctx);
-    k_scan_apply<<<tiles, SCAN_THREADS, 0, st>>>(hist, tile_sums, tiles, offsets, (uint32_t)M);
-    B200_LAUNCH_CHECK(ctx);
-    B200_CUDA(cudaEventRecord(ctx.ev[PH_SCAN + 1], st));
-    // the number of sorted items is known after the scan; it sizes the accumulation segments.
-    // Also read back: the first sorted position of every window (offsets[w * B], one strided copy).
-    uint32_t meta[2] = {0, 0};
-    std::vector<uint32_t> wpos((size_t)W + 1, 0);
-    B200_CUDA(cudaMemcpyAsync(meta, offsets + M, 8, cudaMemcpyDeviceToHost, st));
-    if (!pre)
-        B200_CUDA(cudaMemcpy2DAsync(wpos.data(), 4, offsets, (size_t)B * 4, 4, (size_t)W + 1,
-                                    cudaMemcpyDeviceToHost, st));
-    B200_CUDA(cudaStreamSynchronize(st));
-    const uint32_t total = meta[0];
-    // windows (bucket sets) that hold items
-    // (an earlier range may have used higher windows than this one: meta[1] is cumulative)
-    const int Wu = pre ? 1 : std::max<int>(1, std::min<int>(W, (int)meta[1]));
-    const uint32_t seg = pick_segment<C>(ctx, total);
-    const size_t t1 = ((size_t)total + seg - 1) / seg;
-    uint32_t *seg_bucket;
-    if (!reserve_as(ctx, SL_SEG_BUCKET, (t1 + 1) * 4, &seg_bucket)) return false;
-    // the sorted array is read four items at a time
-    if (!reserve_as(ctx, SL_SORTED, ((size_t)W * n + 4) * sizeof(Entry), &sorted)) return false;
-    // --- scatter
-    k_scatter<C><<<dim3(cdiv(n, 256), W), 256, 0, st>>>(digits, ranks, offsets, sorted, seg_bucket,
-                                                       (uint32_t)n, seg, bstride,
-                                                       pre ? shape->pstride : 1u,
-                                                       pre ? shape->wstride : 0u);
-    B200_LAUNCH_CHECK(ctx);
-    B200_CUDA(cudaEventRecord(ctx.ev[PH_SCATTER + 1], st));
-
-    // --- reduction geometry (Br and K are powers of two, K <= Br).  A single bucket set
-    // (precomputed multiples) is cut into V slices that go through the reduction like V windows.
+    // --- the reduction's scratch (sizes do not depend on the data)
     const uint32_t V = pre ? (B >= 4096 ? 16u : 1u) : 1u;
     const uint32_t Br = B / V;
-    const int Wr = pre ? (int)V : Wu;
     uint32_t K = 16;
     while ((M / K) > 65536 && K < 128) K <<= 1;
     if (ctx.opt_reduce_chunk > 0) K = 1u << std::min(ctx.opt_reduce_chunk, 12);
@@ -264,176 +337,223 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
     uint32_t log2K = 0, log2Br = 0;
     while ((1u << log2K) < K) log2K++;
     while ((1u << log2Br) < Br) log2Br++;
-    uint32_t *chunk_T, *window_T = nullptr, *horner;
-    if (!reserve_as(ctx, SL_CHUNKS, (size_t)Wr * nchunks * R::XW * 4, &chunks)) return false;
-    if (!reserve_as(ctx, SL_CHUNK_TOTALS, (size_t)Wr * nchunks * R::XW * 4, &chunk_T)) return false;
-    if (!reserve_as(ctx, SL_WINDOWS, (size_t)2 * Wr * R::XW * 4, &windows)) return false;
+    const int Wr_max = pre ? (int)V : W;
+    uint32_t *chunks, *chunk_T, *windows, *window_T = nullptr, *horner;
+    if (!reserve_as(ctx, SL_CHUNKS, (size_t)Wr_max * nchunks * R::XW * 4, &chunks)) return false;
+    if (!reserve_as(ctx, SL_CHUNK_TOTALS, (size_t)Wr_max * nchunks * R::XW * 4, &chunk_T)) return false;
+    if (!reserve_as(ctx, SL_WINDOWS, (size_t)2 * Wr_max * R::XW * 4, &windows)) return false;
     if (!reserve_as(ctx, SL_HORNER, (size_t)R::XW * 4, &horner)) return false;
-    if (pre) window_T = windows + (size_t)Wr * R::XW;
+    if (pre) window_T = windows + (size_t)Wr_max * R::XW;
     constexpr int WR_THREADS = 256;
     const size_t wr_smem = (size_t)WR_THREADS * R::XW * 4;
-    static bool attr_set = false;
-    if (!attr_set) {
+    if (!(ctx.attr_mask & (1u << C::ID))) {  // function attributes are per device
         B200_CUDA(cudaFuncSetAttribute(k_window_reduce<C, WR_THREADS>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wr_smem));
-        attr_set = true;
+        ctx.attr_mask |= 1u << C::ID;
     }
-    if (ctx.tail_pending) {  // the previous range's tail reads chunks / chunk_T / windows
+
+    // --- stream choreography.  Sorts run on the sort stream, accumulations alternate between the
+    // main and the second accumulation stream (the partly filled last wave of one launch overlaps
+    // the first wave of the next).  Buffer set p = parity of the sort; ev_sort[p] = "sort into set
+    // p done", ev_sort[2 + p] = "the accumulation that read set p is done".
+    cudaStream_t ss = ctx.sort_stream;
+    B200_CUDA(cudaEventRecord(ctx.ev_group_go, st));
+    if (!ctx.sort_inputs_ready)  // inputs (uploads, ingest) were queued on the main stream
+        B200_CUDA(cudaStreamWaitEvent(ss, ctx.ev_group_go, 0));
+    if (range_first) B200_CUDA(cudaMemsetAsync(used_windows, 0, 4, ss));
+    if (ranged && range_first) B200_CUDA(cudaMemsetAsync(sc.live, 0, M * 4, ss));
+
+    const size_t G = gsizes.size();
+    const uint32_t SEG_CARRY = pick_carry_segment<C>(ctx);
+    size_t toff = 0;      // carry entries written so far (all groups share one carry list)
+    int w_lo = 0;
+    int Wu = W;           // windows that hold items (known after the first digit pass)
+    bool any_items = false;
+    cudaStream_t last_as = st;
+    // sort of group g: queued on the sort stream; returns the group's item count (host sync)
+    struct Sorted {
+        int p;
+        uint32_t total, seg;
+        size_t t1;
+        int lo, hi;
+    };
+    auto sort_group = [&](int lo, int hi, bool first, Sorted &out) -> bool {
+        const int p = ctx.sort_parity;
+        ctx.sort_parity ^= 1;
+        const int wg = hi - lo;
+        const size_t mg = pre ? M : (size_t)wg * B;
+        uint32_t *hist_g = sc.hist + (pre ? 0 : (size_t)lo * B);
+        // (consecutive groups use different buffer sets, so the item count a scan writes behind
+        // its slice never lands in a neighbour's)
+        uint32_t *off_g = sc.offsets[p] + (pre ? 0 : (size_t)lo * B);
+        // the accumulation that last read buffer set p must be done
+        B200_CUDA(cudaStreamWaitEvent(ss, ctx.ev_sort[2 + p], 0));
+        B200_CUDA(cudaMemsetAsync(hist_g, 0, mg * 4, ss));
+        // the first pass walks every window once to find the highest one in use
+        k_digits<C><<<cdiv(n, 256), 256, 0, ss>>>((const uint32_t *)d_scalars, d_inf, sc.digits[p],
+                                                   sc.ranks[p], hist_g, used_windows, (uint32_t)n, c, lo,
+                                                   hi, first ? W : hi, bstride, geo.fold_bit,
+                                                   pre ? shape->pstride : 1u, pre ? shape->wstride : 0u);
+        B200_LAUNCH_CHECK(ctx);
+        if (first) B200_CUDA(cudaEventRecord(ctx.ev[PH_DIGITS + 1], ss));
+        const uint32_t tiles = cdiv(mg, SCAN_TILE);
+        k_scan_tiles<<<tiles, SCAN_THREADS, 0, ss>>>(hist_g, sc.tile_sums, (uint32_t)mg);
+        B200_LAUNCH_CHECK(ctx);
+        k_scan_tile_sums<<<1, 1024, 0, ss>>>(sc.tile_sums, tiles);
+        B200_LAUNCH_CHECK(ctx);
+        k_scan_apply<<<tiles, SCAN_THREADS, 0, ss>>>(hist_g, sc.tile_sums, tiles, off_g, (uint32_t)mg);
+        B200_LAUNCH_CHECK(ctx);
+        if (first) B200_CUDA(cudaEventRecord(ctx.ev[PH_SCAN + 1], ss));
+        // the number of sorted items sizes the accumulation segments
+        uint32_t meta[2] = {0, 0};
+        B200_CUDA(cudaMemcpyAsync(&meta[0], off_g + mg, 4, cudaMemcpyDeviceToHost, ss));
+        B200_CUDA(cudaMemcpyAsync(&meta[1], used_windows, 4, cudaMemcpyDeviceToHost, ss));
+        B200_CUDA(cudaStreamSynchronize(ss));
+        out.p = p, out.lo = lo, out.hi = hi;
+        out.total = meta[0];
+        if (first) Wu = pre ? 1 : std::max<int>(1, std::min<int>(W, (int)meta[1]));
+        // segment length from the parallelism the whole call offers (groups overlap pairwise)
+        const size_t est = G > 1 ? (size_t)out.total * 2 : (size_t)out.total;
+        out.seg = pick_segment<C>(ctx, est);
+        out.t1 = ((size_t)out.total + out.seg - 1) / out.seg;
+        if (out.total > 0) {
+            k_scatter<C><<<dim3(cdiv(n, 256), wg), 256, 0, ss>>>(
+                sc.digits[p], sc.ranks[p], off_g, sc.sorted[p], sc.seg_bucket[p], (uint32_t)n, out.seg,
+                bstride, pre ? shape->pstride : 1u, pre ? shape->wstride : 0u);
+            B200_LAUNCH_CHECK(ctx);
+        }
+        if (first) B200_CUDA(cudaEventRecord(ctx.ev[PH_SCATTER + 1], ss));
+        B200_CUDA(cudaEventRecord(ctx.ev_sort[p], ss));
+        return true;
+    };
+    auto accumulate_group = [&](const Sorted &sg, size_t g) -> bool {
+        cudaStream_t as = (g & 1) ? ctx.acc_stream : st;
+        last_as = as;
+        B200_CUDA(cudaStreamWaitEvent(as, ctx.ev_sort[sg.p], 0));
+        if (g == 1) {  // the second stream joins: it must not run ahead of the call's start
+            B200_CUDA(cudaStreamWaitEvent(as, ctx.ev_group_go, 0));
+        }
+        if (sg.total > 0) {
+            any_items = true;
+            if (toff + sg.t1 > sc.carry_cap) {
+                set_error("multi_exp: carry list overflow (%zu + %zu > %zu)", toff, sg.t1, sc.carry_cap);
+                return false;
+            }
+            const uint32_t *off_g = sc.offsets[sg.p] + (pre ? 0 : (size_t)sg.lo * B);
+            uint32_t *bk = buckets + (pre ? 0 : (size_t)sg.lo * B * R::XW);
+            const uint32_t key_base = pre ? 0u : (uint32_t)sg.lo * B;
+            if (ranged)
+                k_accum_first_merge<C><<<cdiv(sg.t1, 128), 128, 0, as>>>(
+                    sc.sorted[sg.p], off_g, sc.seg_bucket[sg.p], sg.total, sg.seg, 0u, (uint32_t)sg.t1,
+                    (const uint32_t *)d_aff, bk, sc.keyA + toff, sc.ptA + toff * R::XW, key_base, sc.live);
+            else
+                k_accum_first<C><<<cdiv(sg.t1, 128), 128, 0, as>>>(
+                    sc.sorted[sg.p], off_g, sc.seg_bucket[sg.p], sg.total, sg.seg, 0u, (uint32_t)sg.t1,
+                    (const uint32_t *)d_aff, bk, sc.keyA + toff, sc.ptA + toff * R::XW, key_base);
+            B200_LAUNCH_CHECK(ctx);
+            toff += sg.t1;
+        }
+        B200_CUDA(cudaEventRecord(ctx.ev_sort[2 + sg.p], as));
+        return true;
+    };
+
+    if (ctx.tail_pending && !ranged) {  // the previous chunk's tail reads chunks / chunk_T / windows
         B200_CUDA(cudaStreamWaitEvent(st, ctx.ev_tail_done, 0));
         ctx.tail_pending = false;
     }
-
-    // --- groups of windows, walked from the top window down.  The accumulation of a group is one
-    // launch of k_accum_first over the group's segments; everything after it -- carry rounds,
-    // bucket reduction, window totals, the group's stretch of the Horner chain -- is a string of
-    // small or latency-bound kernels that runs on the high-priority side stream UNDER the
-    // accumulation of the next group.  Only the bottom group's string (one window) is exposed.
-    // Consecutive accumulations alternate between two streams so that the last, partly filled
-    // wave of one launch overlaps the first wave of the next.
-    struct Group {
-        int lo, hi;  // windows [lo, hi)
-    };
-    std::vector<Group> groups;  // top-down
-    if (pre || total == 0 || ranged) {
-        groups.push_back(Group{0, Wr});
-    } else {
-        int ng = ctx.opt_window_groups;
-        std::vector<int> sizes;  // bottom-up
-        // Measured (profiles/groups_sweep_r01d.log): more than one group does not pay.  The strings
-        // of small kernels are chains of dependent field products; next to an accumulation that
-        // saturates the multiply pipe of every SM their warps wait for issue slots and the chains
-        // stretch more than the overlap hides (2^24 alt_bn128 G1: 42.5 ms with one group, 48.6 with
-        // six; bw6_761 2^19: 50 against 95 ms).  The default is therefore ONE group; the option
-        // stays for experiments (an SM partition reserved for the side stream would change this).
-        if (ng == 0) ng = 1;
-        if (ng == 1 || Wu == 1) {
-            sizes.push_back(Wu);
-        } else if (ng > 1 && ng < 64) {
-            for (int g = 0; g < std::min(ng, Wu); g++) sizes.push_back(0);
-            for (int w = 0; w < Wu; w++) sizes[(size_t)w * sizes.size() / Wu]++;
-        } else {  // 64: 1, 1, 2, then threes (bottom-up)
-            int left = Wu;
-            for (int want : {1, 1, 2}) {
-                if (left <= 0) break;
-                sizes.push_back(std::min(want, left));
-                left -= sizes.back();
-            }
-            while (left > 0) {
-                sizes.push_back(std::min(3, left));
-                left -= sizes.back();
-            }
-        }
-        int hi = Wu;
-        for (size_t g = sizes.size(); g-- > 0;) {
-            groups.push_back(Group{hi - sizes[g], hi});
-            hi -= sizes[g];
-        }
+    // group 0 is sorted up front; from then on: sort g + 1 is queued, then accumulation g
+    Sorted cur, nxt;
+    if (!sort_group(0, gsizes[0], true, cur)) return false;
+    if (ctx.tail_pending) {  // ranged: the previous range's carry rounds add into the same buckets
+        B200_CUDA(cudaStreamWaitEvent(st, ctx.ev_tail_done, 0));
+        ctx.tail_pending = false;
     }
-    const size_t G = groups.size();
-    // tails on the side stream; for a range that is not the last one the "tail" is its carry
-    // rounds, which run under the digit pass and the sort of the next range
-    const bool side = G > 1 || ctx.defer_tail || (ranged && !range_last);
-    cudaStream_t ts = side ? ctx.tail_stream : st;
-    const uint32_t SEG_CARRY = pick_carry_segment<C>(ctx);
-    uint32_t *keyA = nullptr, *ptA = nullptr, *keyB = nullptr, *ptB = nullptr, *keyC = nullptr, *ptC = nullptr;
-    if (total > 0) {
-        const size_t t2 = (t1 + 1 + SEG_CARRY - 1) / SEG_CARRY, t3 = (t2 + SEG_CARRY - 1) / SEG_CARRY;
-        if (!reserve_as(ctx, SL_CARRY_KEY_A, t1 * 4, &keyA)) return false;
-        if (!reserve_as(ctx, SL_CARRY_PT_A, t1 * R::XW * 4, &ptA)) return false;
-        if (!reserve_as(ctx, SL_CARRY_KEY_B, t2 * 4, &keyB)) return false;
-        if (!reserve_as(ctx, SL_CARRY_PT_B, t2 * R::XW * 4, &ptB)) return false;
-        if (!reserve_as(ctx, SL_CARRY_KEY_C, t3 * 4, &keyC)) return false;
-        if (!reserve_as(ctx, SL_CARRY_PT_C, t3 * R::XW * 4, &ptC)) return false;
-    }
-    if (G > 1) {
-        B200_CUDA(cudaEventRecord(ctx.ev_group_go, st));
-        B200_CUDA(cudaStreamWaitEvent(ctx.acc_stream, ctx.ev_group_go, 0));
-    }
-    // segment that holds the first item of window w (the segment straddling two windows belongs
-    // to the upper one)
-    auto seg_of_window = [&](int w) -> uint32_t { return w <= 0 ? 0u : wpos[(size_t)w] / seg; };
+    w_lo = gsizes[0];
     for (size_t g = 0; g < G; g++) {
-        const Group &gr = groups[g];
-        const bool first = g == 0, last = g + 1 == G;
-        cudaStream_t as = (g & 1) ? ctx.acc_stream : st;
-        if (total > 0) {
-            const uint32_t tb = (pre || last) ? 0u : seg_of_window(gr.lo);
-            const uint32_t te = (pre || first) ? (uint32_t)t1 : seg_of_window(gr.hi);
-            if (te > tb) {
-                if (ranged)
-                    k_accum_first_merge<C><<<cdiv(te - tb, 128), 128, 0, as>>>(
-                        sorted, offsets, seg_bucket, total, seg, tb, te, (const uint32_t *)d_aff,
-                        buckets, keyA, ptA, live);
-                else
-                    k_accum_first<C><<<cdiv(te - tb, 128), 128, 0, as>>>(
-                        sorted, offsets, seg_bucket, total, seg, tb, te, (const uint32_t *)d_aff,
-                        buckets, keyA, ptA);
-                B200_LAUNCH_CHECK(ctx);
-            }
-            if (side) {
-                B200_CUDA(cudaEventRecord(ctx.ev_group[g & 1], as));
-                B200_CUDA(cudaStreamWaitEvent(ts, ctx.ev_group[g & 1], 0));
-            }
-            if (last) B200_CUDA(cudaEventRecord(ctx.ev[PH_ACCUM + 1], as));
-            // carry rounds over entries [tb, te] (both boundary entries; each is live in one group)
-            const uint32_t cb = tb, ce = std::min<uint32_t>((uint32_t)t1, te + 1);
-            const uint32_t key_lo = pre ? 0u : (uint32_t)gr.lo * B;
-            const uint32_t key_hi = pre ? CARRY_DEAD : (uint32_t)gr.hi * B;
-            const uint32_t *kin = keyA, *pin = ptA;
-            uint32_t *kout = keyB, *pout = ptB;
-            uint32_t begin = cb, endp = ce;
-            while (endp > begin) {
-                const size_t tn = ((size_t)(endp - begin) + SEG_CARRY - 1) / SEG_CARRY;
-                k_accum_carry<C><<<cdiv(tn, 128), 128, 0, ts>>>(kin, pin, begin, endp, key_lo, key_hi,
-                                                                SEG_CARRY, buckets, kout, pout);
-                B200_LAUNCH_CHECK(ctx);
-                if (tn == 1) break;  // a single thread owns every run it sees: no carries remain
-                kin = kout, pin = pout;
-                kout = (kout == keyB) ? keyC : keyB;
-                pout = (pout == ptB) ? ptC : ptB;
-                begin = 0, endp = (uint32_t)tn;
-            }
-        } else if (last) {
-            B200_CUDA(cudaEventRecord(ctx.ev[PH_ACCUM + 1], st));
+        bool have_next = false;
+        if (g + 1 < G && w_lo < Wu) {  // windows from Wu up hold no items
+            const int hi = std::min(w_lo + gsizes[g + 1], Wu);
+            if (!sort_group(w_lo, hi, false, nxt)) return false;
+            w_lo = hi;
+            have_next = true;
         }
-        if (!side) B200_CUDA(cudaEventRecord(ctx.ev[PH_CARRY + 1], st));
-        if (!range_last) break;  // the buckets stay; the next range of the call adds to them
-        // bucket reduction, window totals, Horner stretch of this group
-        k_bucket_reduce<C><<<dim3(cdiv(nchunks, 64), gr.hi - gr.lo), 64, 0, ts>>>(
-            buckets, ranged ? live : hist, Br, K, (uint32_t)gr.lo, chunks, chunk_T);
-        B200_LAUNCH_CHECK(ctx);
-        if (!side) B200_CUDA(cudaEventRecord(ctx.ev[PH_BUCKET_REDUCE + 1], st));
-        if (last && ctx.defer_tail) {
-            // the next range's digit pass rewrites hist / buckets: it may start from here on
-            B200_CUDA(cudaEventRecord(ctx.ev_tail_go, ts));
-            B200_CUDA(cudaStreamWaitEvent(st, ctx.ev_tail_go, 0));
-        }
-        k_window_reduce<C, WR_THREADS><<<gr.hi - gr.lo, WR_THREADS, wr_smem, ts>>>(
-            chunks, chunk_T, nchunks, log2K, (uint32_t)gr.lo, windows, window_T);
-        B200_LAUNCH_CHECK(ctx);
-        if (pre)
-            k_final_slices<C><<<1, 32, 0, ts>>>(windows, window_T, (int)V, (int)log2Br, (uint32_t *)d_out);
-        else
-            k_final<C><<<1, 32, 0, ts>>>(windows, gr.lo, gr.hi, c, horner, first, last, (uint32_t *)d_out);
-        B200_LAUNCH_CHECK(ctx);
+        if (!accumulate_group(cur, g)) return false;
+        if (!have_next) break;
+        cur = nxt;
     }
-    if (G > 1 && (G & 1) == 0) {
-        // the last accumulation ran on the second stream: the caller's stream must see it
-        // (ev_group[1] was recorded after it)
+    if (last_as != st) {  // the main stream continues after the last accumulation
+        B200_CUDA(cudaEventRecord(ctx.ev_group[1], last_as));
         B200_CUDA(cudaStreamWaitEvent(st, ctx.ev_group[1], 0));
     }
-    if (side) {
-        B200_CUDA(cudaEventRecord(ctx.ev_tail_done, ts));
-        if (ctx.defer_tail || (ranged && !range_last)) {
-            ctx.tail_pending = true;
-        } else {
-            B200_CUDA(cudaStreamWaitEvent(st, ctx.ev_tail_done, 0));
+    if (G > 1) {  // ... and after the other stream's
+        B200_CUDA(cudaStreamWaitEvent(st, ctx.ev_sort[2], 0));
+        B200_CUDA(cudaStreamWaitEvent(st, ctx.ev_sort[3], 0));
+    } else {
+        B200_CUDA(cudaStreamWaitEvent(st, ctx.ev_sort[2 + cur.p], 0));
+    }
+    B200_CUDA(cudaEventRecord(ctx.ev[PH_ACCUM + 1], st));
+
+    // tails on the side stream: for a range that is not the last one the "tail" is its carry
+    // rounds, which run under the digit pass and the sort of the next range; for a deferred chunk
+    // (streamed MSM) everything after the bucket reduction
+    const bool side = ctx.defer_tail || (ranged && !range_last);
+    cudaStream_t ts = (ranged && !range_last) ? ctx.tail_stream : st;
+    if (ts != st) {
+        B200_CUDA(cudaEventRecord(ctx.ev_group[0], st));
+        B200_CUDA(cudaStreamWaitEvent(ts, ctx.ev_group[0], 0));
+    }
+    // --- carry rounds over the whole carry list (keys ascending across the groups)
+    if (any_items) {
+        const uint32_t *kin = sc.keyA, *pin = sc.ptA;
+        uint32_t *kout = sc.keyB, *pout = sc.ptB;
+        uint32_t begin = 0, endp = (uint32_t)toff;
+        while (endp > begin) {
+            const size_t tn = ((size_t)(endp - begin) + SEG_CARRY - 1) / SEG_CARRY;
+            k_accum_carry<C><<<cdiv(tn, 128), 128, 0, ts>>>(kin, pin, begin, endp, 0u, CARRY_DEAD,
+                                                            SEG_CARRY, buckets, kout, pout);
+            B200_LAUNCH_CHECK(ctx);
+            if (tn == 1) break;  // a single thread owns every run it sees: no carries remain
+            kin = kout, pin = pout;
+            kout = (kout == sc.keyB) ? sc.keyC : sc.keyB;
+            pout = (pout == sc.ptB) ? sc.ptC : sc.ptB;
+            begin = 0, endp = (uint32_t)tn;
         }
     }
-    if (side) {  // overlapped: what is left after the last accumulation counts as carry rounds
-        B200_CUDA(cudaEventRecord(ctx.ev[PH_CARRY + 1], st));
+    B200_CUDA(cudaEventRecord(ctx.ev[PH_CARRY + 1], st));
+    if (!range_last) {  // the buckets stay; the next range of the call adds to them
+        B200_CUDA(cudaEventRecord(ctx.ev_tail_done, ts));
+        ctx.tail_pending = true;
         B200_CUDA(cudaEventRecord(ctx.ev[PH_BUCKET_REDUCE + 1], st));
+        B200_CUDA(cudaEventRecord(ctx.ev[PH_FINAL + 1], st));
+        return true;
     }
+    // --- bucket reduction, window totals, Horner
+    const int Wr = pre ? (int)V : Wu;
+    k_bucket_reduce<C><<<dim3(cdiv(nchunks, 64), Wr), 64, 0, st>>>(
+        buckets, ranged ? sc.live : sc.hist, Br, K, 0u, chunks, chunk_T);
+    B200_LAUNCH_CHECK(ctx);
+    B200_CUDA(cudaEventRecord(ctx.ev[PH_BUCKET_REDUCE + 1], st));
+    cudaStream_t fs = st;
+    if (ctx.defer_tail) {
+        // the next chunk's digit pass rewrites hist / buckets: it may start from here on, the
+        // latency-bound window totals and the Horner chain move to the side stream
+        fs = ctx.tail_stream;
+        B200_CUDA(cudaEventRecord(ctx.ev_tail_go, st));
+        B200_CUDA(cudaStreamWaitEvent(fs, ctx.ev_tail_go, 0));
+    }
+    k_window_reduce<C, WR_THREADS><<<Wr, WR_THREADS, wr_smem, fs>>>(chunks, chunk_T, nchunks, log2K, 0u,
+                                                                    windows, window_T);
+    B200_LAUNCH_CHECK(ctx);
+    if (pre)
+        k_final_slices<C><<<1, 32, 0, fs>>>(windows, window_T, (int)V, (int)log2Br, (uint32_t *)d_out);
+    else
+        k_final<C><<<1, 32, 0, fs>>>(windows, 0, Wr, c, horner, true, true, (uint32_t *)d_out);
+    B200_LAUNCH_CHECK(ctx);
+    if (ctx.defer_tail) {
+        B200_CUDA(cudaEventRecord(ctx.ev_tail_done, fs));
+        ctx.tail_pending = true;
+    }
+    (void)side;
     B200_CUDA(cudaEventRecord(ctx.ev[PH_FINAL + 1], st));
     return true;
 }
@@ -443,41 +563,75 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
 // device: c doublings per step in XYZZ, one batch normalisation per multiple.
 template <class C>
 bool precompute_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, size_t n, int c, int W,
-                     void *d_table) {
+                     void *d_table, uint8_t *d_table_inf) {
     using R = Raw<C>;
     if (n == 0 || W <= 0) return true;
     uint32_t *state, *raw;
-    uint8_t *inf_scratch;
     if (!reserve_as(ctx, SL_PRE_STATE, n * R::XW * 4, &state)) return false;
     if (!reserve_as(ctx, SL_PRE_RAW, n * R::PW * 4, &raw)) return false;
-    if (!reserve_as(ctx, SL_TABLE_INF, n, &inf_scratch)) return false;
     uint32_t *table = (uint32_t *)d_table;
     B200_CUDA(cudaMemcpyAsync(table, d_aff, n * R::AW * 4, cudaMemcpyDeviceToDevice, ctx.stream));
+    B200_CUDA(cudaMemcpyAsync(d_table_inf, d_inf, n, cudaMemcpyDeviceToDevice, ctx.stream));
     for (int w = 1; w < W; w++) {
         k_pre_step<C><<<cdiv(n, 128), 128, 0, ctx.stream>>>((const uint32_t *)d_aff, d_inf, state, raw,
                                                             (uint32_t)n, c, w == 1);
         B200_LAUNCH_CHECK(ctx);
-        if (!normalise_dev<C>(ctx, raw, n, nullptr, table + (size_t)w * n * R::AW, inf_scratch))
+        // a multiple of a point of small even order (unchecked input in a cofactor group) can be
+        // the zero element although the base is not: every multiple keeps its own flag
+        if (!normalise_dev<C>(ctx, raw, n, nullptr, table + (size_t)w * n * R::AW,
+                              d_table_inf + (size_t)w * n))
             return false;
     }
     return true;
 }
 
+// ---- fixed-base exponentiation (multiexp.tcc:809-947) ----------------------------------------
 template <class C>
-bool batch_exp_impl(Ctx &ctx, const void *d_table_raw, size_t rows, size_t row_len, int window,
-                    const void *d_scalars, size_t n, void *d_out) {
-    using R = Raw<C>;
-    const size_t entries = rows * row_len;
-    uint32_t *taff;
+bool table_normalise_impl(Ctx &ctx, const void *d_table_raw, size_t entries, void *d_table_aff) {
     uint8_t *tinf;
-    if (!reserve_as(ctx, SL_TABLE_AFF, entries * R::AW * 4, &taff)) return false;
     if (!reserve_as(ctx, SL_TABLE_INF, entries, &tinf)) return false;
-    // table entries are arbitrary Jacobian/projective representatives: normalise once
-    if (!normalise_dev<C>(ctx, (const uint32_t *)d_table_raw, entries, nullptr, taff, tinf)) return false;
+    // table entries are arbitrary Jacobian / projective representatives: normalised once per table
+    return normalise_dev<C>(ctx, (const uint32_t *)d_table_raw, entries, nullptr,
+                            (uint32_t *)d_table_aff, tinf);
+}
+
+// get_window_table (multiexp.tcc:809-846) on the device: entry [r][j] = j 2^(r w) g for j below
+// the row's length (the last row is shorter, :815; its tail stays zero), reference layout.
+template <class C>
+bool table_build_impl(Ctx &ctx, const void *d_g_raw, int scalar_bits, int window, size_t rows,
+                      size_t row_len, void *d_table_raw) {
+    using R = Raw<C>;
+    uint32_t *row_base;
+    if (!reserve_as(ctx, SL_PRE_STATE, rows * R::XW * 4, &row_base)) return false;
+    k_table_row_bases<C><<<cdiv(rows, 32), 32, 0, ctx.stream>>>((const uint32_t *)d_g_raw, window,
+                                                                (uint32_t)rows, row_base);
+    B200_LAUNCH_CHECK(ctx);
+    const uint32_t last_len = 1u << (scalar_bits - (int)(rows - 1) * window);
+    const uint32_t blocks_per_row = cdiv(row_len, TABLE_RUN);
+    const size_t threads = rows * blocks_per_row;
+    k_table_fill<C><<<cdiv(threads, 64), 64, 0, ctx.stream>>>(row_base, (uint32_t)rows,
+                                                              (uint32_t)row_len, last_len,
+                                                              (uint32_t *)d_table_raw);
+    B200_LAUNCH_CHECK(ctx);
+    return true;
+}
+
+template <class C>
+bool table_export_impl(Ctx &ctx, const void *d_table_aff, size_t entries, void *d_table_raw) {
+    if (entries == 0) return true;
+    k_affine_to_special<C><<<cdiv(entries, 128), 128, 0, ctx.stream>>>(
+        (const uint32_t *)d_table_aff, (uint32_t *)d_table_raw, (uint32_t)entries);
+    B200_LAUNCH_CHECK(ctx);
+    return true;
+}
+
+template <class C>
+bool batch_exp_impl(Ctx &ctx, const void *d_table_aff, size_t rows, size_t row_len, int window,
+                    const void *d_scalars, const void *d_coeff, size_t n, void *d_out) {
     if (n == 0) return true;
-    k_batch_exp<C><<<cdiv(n, 128), 128, 0, ctx.stream>>>((const uint32_t *)d_scalars, taff,
-                                                         (uint32_t)rows, (uint32_t)row_len, window,
-                                                         (uint32_t *)d_out, (uint32_t)n);
+    k_batch_exp<C><<<cdiv(n, 128), 128, 0, ctx.stream>>>(
+        (const uint32_t *)d_scalars, (const uint32_t *)d_coeff, (const uint32_t *)d_table_aff,
+        (uint32_t)rows, (uint32_t)row_len, window, (uint32_t *)d_out, (uint32_t)n);
     B200_LAUNCH_CHECK(ctx);
     return true;
 }
@@ -548,10 +702,14 @@ const GroupOps *make_ops() {
                                  C::Fr::Params::BITS,
                                  &ingest_impl<C>,
                                  &msm_impl<C>,
+                                 &msm_prepare_impl<C>,
                                  &precompute_impl<C>,
                                  &stream_decode_impl<C>,
                                  &sum_impl<C>,
                                  &to_special_impl<C>,
+                                 &table_normalise_impl<C>,
+                                 &table_build_impl<C>,
+                                 &table_export_impl<C>,
                                  &batch_exp_impl<C>,
                                  &window_bits_impl<C>,
                                  &wire_decode_impl<C>,

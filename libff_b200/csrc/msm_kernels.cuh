@@ -44,6 +44,23 @@ __global__ void k_ingest_special(const uint32_t *__restrict__ raw, uint32_t *__r
     inf_flag[i] = inf;
 }
 
+// packed upload: the array already holds device-affine records; only the flags are derived
+template <class C>
+__global__ void k_flags_from_affine(const uint32_t *__restrict__ aff, uint8_t *__restrict__ inf_flag,
+                                    uint32_t n) {
+    using R = Raw<C>;
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint4 *p = reinterpret_cast<const uint4 *>(aff + (size_t)i * R::AW);
+    uint32_t acc = 0;
+#pragma unroll
+    for (int k = 0; k < R::AW / 4; k++) {
+        const uint4 v = p[k];
+        acc |= v.x | v.y | v.z | v.w;
+    }
+    inf_flag[i] = acc == 0;
+}
+
 // ------------------------------------------------------------------------------------------
 // Warp-aggregated counter updates: lanes that hit the same bucket (witness-like inputs put a
 // large share of all scalars into one bucket) issue ONE atomic between them.  Must be called by
@@ -69,22 +86,31 @@ __device__ __forceinline__ uint32_t warp_cursor_take(uint32_t *cursor, bool vali
 // ------------------------------------------------------------------------------------------
 // scalars -> signed digits + histogram.  digits[w * n + i] in [-2^(c-1), 2^(c-1)]
 // bstride = buckets per window (2^(c-1)), or 0 when all windows share ONE bucket set (precomputed
-// multiples 2^(w c) P_i, multiexp_stream.tcc:124-162).  fold_bit >= 0: W c equals the scalar
-// width, so a scalar with bit W c - 1 set would carry out of the top digit (the reference's
-// field_get_signed_digits drops that carry, field_utils.tcc:205-239); such a scalar is replaced
-// by r - s, whose top digit is small, and all its digits change sign: s P = -(r - s) P.
+// multiples 2^(w c) P_i, multiexp_stream.tcc:124-162); inf_flag then holds one flag per table
+// entry (i * pstride + w * wstride) instead of one per base.
+// Windows [w_lo, w_hi) are emitted (a group of windows of one MSM; the carry chain below w_lo is
+// walked without output) into digits[(w - w_lo) * n + i]; their buckets are (w - w_lo) * bstride + ..
+// The walk continues to w_top >= w_hi without output, only to find the highest window in use.
+// fold_bit >= 0: W c equals the scalar width, so a scalar with bit W c - 1 set would carry out of
+// the top digit (the reference's field_get_signed_digits drops that carry, field_utils.tcc:205-239);
+// such a scalar is replaced by r - s, whose top digit is small, and all its digits change sign:
+// s P = -(r - s) P.  fold_bit == -2: the reference's own recoding instead (a digit of exactly
+// 2^(c-1) becomes -2^(c-1) with a carry, field_utils.tcc:224-236) and the carry out of the top
+// digit is dropped as the reference drops it.
 template <class C>
 __global__ void k_digits(const uint32_t *__restrict__ scalars, const uint8_t *__restrict__ inf_flag,
                          int32_t *__restrict__ digits, uint32_t *__restrict__ ranks,
                          uint32_t *__restrict__ hist, uint32_t *__restrict__ used_windows,
-                         uint32_t n, int c, int W, uint32_t bstride, int fold_bit) {
+                         uint32_t n, int c, int w_lo, int w_hi, int w_top, uint32_t bstride,
+                         int fold_bit, uint32_t pstride, uint32_t wstride) {
     using Fr = typename C::Fr;
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t top = 0;  // 1 + index of the highest window with a non-zero digit
     {
         const bool live = i < n;  // every lane runs the loop: the histogram update is warp-wide
         Fr s = live ? Fr::from_mont(Fr::load(scalars + (size_t)i * Fr::N)) : Fr::zero();
-        bool skip = !live || (inf_flag != nullptr && inf_flag[i]);
+        const bool per_entry = bstride == 0;
+        bool skip = !live || (!per_entry && inf_flag != nullptr && inf_flag[i]);
         bool flip = false;
         if (fold_bit >= 0) {
             uint32_t word = 0;
@@ -95,23 +121,32 @@ __global__ void k_digits(const uint32_t *__restrict__ scalars, const uint8_t *__
             if (flip) s = Fr::neg(s);
         }
         const uint32_t mask = (1u << c) - 1, half = 1u << (c - 1);
+        const uint32_t tie = fold_bit == -2 ? 1u : 0u;  // reference recoding: 2^(c-1) carries
         uint32_t carry = 0;
-        for (int w = 0; w < W; w++) {
+        for (int w = 0; w < w_top; w++) {
             uint32_t d = (s.v[0] & mask) + carry;
-            carry = d > half;
+            carry = d + tie > half;
             int32_t sd = (int32_t)d - (int32_t)(carry << c);
-            if (flip) sd = -sd;
+#pragma unroll
+            for (int k = 0; k < Fr::N - 1; k++) s.v[k] = __funnelshift_r(s.v[k], s.v[k + 1], c);
+            s.v[Fr::N - 1] >>= c;
             if (skip) sd = 0;
-            if (live) digits[(size_t)w * n + i] = sd;
+            if (w < w_lo || w >= w_hi) {  // uniform across the block
+                if (sd != 0) top = w + 1;
+                continue;
+            }
+            if (flip) sd = -sd;
+            if (per_entry && sd != 0 && inf_flag != nullptr &&
+                inf_flag[(size_t)i * pstride + (size_t)w * wstride])
+                sd = 0;
+            const size_t slot = (size_t)(w - w_lo) * n + i;
+            if (live) digits[slot] = sd;
             if (sd != 0) top = w + 1;
             // the counter's value before this item = the item's rank inside its bucket: the
             // scatter then needs no second round of atomics
             const uint32_t rank = warp_cursor_take(
-                hist, sd != 0, (uint32_t)w * bstride + (uint32_t)(sd < 0 ? -sd : sd) - 1);
-            if (live) ranks[(size_t)w * n + i] = rank;
-#pragma unroll
-            for (int k = 0; k < Fr::N - 1; k++) s.v[k] = __funnelshift_r(s.v[k], s.v[k + 1], c);
-            s.v[Fr::N - 1] >>= c;
+                hist, sd != 0, (uint32_t)(w - w_lo) * bstride + (uint32_t)(sd < 0 ? -sd : sd) - 1);
+            if (live) ranks[slot] = rank;
         }
     }
     // the reference sizes its loop by the longest scalar (num_bits, multiexp.tcc:298-306); here
@@ -247,7 +282,8 @@ __device__ __forceinline__ void accum_first_body(
     const Entry *__restrict__ sorted, const uint32_t *__restrict__ offsets,
     const uint32_t *__restrict__ seg_bucket, uint32_t total, uint32_t SEG, uint32_t t_begin,
     uint32_t t_end, const uint32_t *__restrict__ aff, uint32_t *__restrict__ bucket_acc,
-    uint32_t *__restrict__ carry_key, uint32_t *__restrict__ carry_pt, uint32_t *live) {
+    uint32_t *__restrict__ carry_key, uint32_t *__restrict__ carry_pt, uint32_t key_base,
+    uint32_t *live) {
     using R = Raw<C>;
     using F = AccumField<typename C::Fq>;
     using X = XYZZ<F>;
@@ -263,7 +299,7 @@ __device__ __forceinline__ void accum_first_body(
     uint32_t cur = seg_bucket[t];
     uint32_t next = offsets[cur + 1];            // first position of the following bucket
     bool head_carry = start > offsets[cur];      // the bucket began in an earlier segment
-    carry_key[t] = cur;
+    carry_key[t] = key_base + cur;  // buckets are local to the launch's window group, keys global
     bool carried = false;
     X acc = X::inf();
     if (MERGE) {
@@ -323,9 +359,9 @@ __global__ void __launch_bounds__(128)
                   const uint32_t *__restrict__ seg_bucket, uint32_t total, uint32_t SEG,
                   uint32_t t_begin, uint32_t t_end, const uint32_t *__restrict__ aff,
                   uint32_t *__restrict__ bucket_acc, uint32_t *__restrict__ carry_key,
-                  uint32_t *__restrict__ carry_pt) {
+                  uint32_t *__restrict__ carry_pt, uint32_t key_base) {
     accum_first_body<C, false>(sorted, offsets, seg_bucket, total, SEG, t_begin, t_end, aff,
-                               bucket_acc, carry_key, carry_pt, nullptr);
+                               bucket_acc, carry_key, carry_pt, key_base, nullptr);
 }
 
 template <class C>
@@ -334,9 +370,10 @@ __global__ void __launch_bounds__(128, Raw<C>::XW <= 32 ? 4 : 1)
                         const uint32_t *__restrict__ seg_bucket, uint32_t total, uint32_t SEG,
                         uint32_t t_begin, uint32_t t_end, const uint32_t *__restrict__ aff,
                         uint32_t *__restrict__ bucket_acc, uint32_t *__restrict__ carry_key,
-                        uint32_t *__restrict__ carry_pt, uint32_t *__restrict__ live) {
+                        uint32_t *__restrict__ carry_pt, uint32_t key_base,
+                        uint32_t *__restrict__ live) {
     accum_first_body<C, true>(sorted, offsets, seg_bucket, total, SEG, t_begin, t_end, aff,
-                              bucket_acc, carry_key, carry_pt, live);
+                              bucket_acc, carry_key, carry_pt, key_base, live);
 }
 
 // Later rounds: the carry list (keys ascending, one XYZZ point each) is reduced the same way with
@@ -391,18 +428,6 @@ __global__ void __launch_bounds__(128)
 }
 
 // ------------------------------------------------------------------------------------------
-// k * p for a small non-negative k (double-and-add, MSB first)
-template <class F>
-__device__ __noinline__ XYZZ<F> small_mul(const XYZZ<F> &p, uint32_t k) {
-    XYZZ<F> r = XYZZ<F>::inf();
-    if (k == 0 || p.is_inf()) return r;
-    for (int bit = 31 - __clz(k); bit >= 0; bit--) {
-        r = XYZZ<F>::dbl(r);
-        if ((k >> bit) & 1) XYZZ<F>::add(r, p);
-    }
-    return r;
-}
-
 // Bucket reduction in two levels of running sums (multiexp.tcc:90-125, 354-376 is the serial
 // form).  With chunks of K buckets and (b + 1) = (b - jK + 1) + jK:
 //   window sum = sum_j L_j + K * sum_j j T_j,   L_j = sum_{b in chunk j} (b - jK + 1) bucket[b],

@@ -429,6 +429,42 @@ def walk_expected_scalar(group: Group, scalars_plain, start: int = 0) -> int:
     return (a * s0 + d * s1) % r
 
 
+def weighted_scalar_sums(group: Group, scalars_mont: np.ndarray, start: int = 0):
+    """(sum_i s_i, sum_i (start + i) s_i) mod r for Montgomery-form scalar rows (numpy uint64,
+    n x limbs), vectorised so that 2^26 scalars take seconds: the Montgomery factor R comes out
+    of the sums, the 64-bit limbs are split into 16-bit pieces and the index-weighted sums are
+    taken over runs of 2^16 rows, which keeps every partial sum below 2^64."""
+    r = group.fr.p
+    a = np.ascontiguousarray(scalars_mont, dtype=np.uint64)
+    n, limbs = a.shape
+    s0 = 0
+    s1 = 0
+    RUN = 1 << 16
+    for lo in range(0, n, RUN):
+        blk = a[lo:lo + RUN]
+        idx = np.arange(blk.shape[0], dtype=np.uint64)  # < 2^16
+        b0 = 0
+        b1 = 0
+        for j in range(limbs):
+            col = blk[:, j]
+            for q in range(4):
+                piece = (col >> np.uint64(16 * q)) & np.uint64(0xFFFF)   # < 2^16
+                sh = 64 * j + 16 * q
+                b0 += int(piece.sum(dtype=np.uint64)) << sh              # < 2^32
+                b1 += int((piece * idx).sum(dtype=np.uint64)) << sh      # < 2^48
+        s0 += b0
+        s1 += b1 + (start + lo) * b0
+    rinv = pow(1 << (64 * limbs), -1, r)
+    return (s0 * rinv) % r, (s1 * rinv) % r
+
+
+def walk_expected_scalar_fast(group: Group, scalars_mont: np.ndarray, start: int = 0) -> int:
+    """walk_expected_scalar on the Montgomery-form limb rows directly (any n up to 2^32)."""
+    a, d = walk_params(group)
+    s0, s1 = weighted_scalar_sums(group, scalars_mont, start)
+    return (a * s0 + d * s1) % group.fr.p
+
+
 # ----------------------------------------------------------------------------------------------
 # Window-size and digit helpers (restating the reference's integer arithmetic)
 

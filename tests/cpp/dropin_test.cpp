@@ -171,10 +171,41 @@ template<typename GroupT> void test_batch_exp(size_t n, size_t window)
     }
     const std::vector<GroupT> part = batch_exp(scalar_size, window, table, v, n / 2);
     CHECK(part.size() == n / 2);
-    // batch_exp_with_coeff (multiexp.tcc:917-947) stays on the CPU and must agree
-    const std::vector<GroupT> coeff = batch_exp_with_coeff(scalar_size, window, table, Field::one(), v);
-    for (size_t i = 0; i < n; ++i) {
-        CHECK(coeff[i] == got[i]);
+    // batch_exp_with_coeff (multiexp.tcc:917-947): on the device too (one Fr product ahead of the
+    // digits); expected values from the reference's windowed_exp on the CPU
+    const std::vector<GroupT> unit = batch_exp_with_coeff(scalar_size, window, table, Field::one(), v);
+    const Field c = SHA512_rng<Field>(77);
+    const std::vector<GroupT> scaled = batch_exp_with_coeff(scalar_size, window, table, c, v);
+    CHECK(unit.size() == n && scaled.size() == n);
+    for (size_t i = 0; i < n && i < scaled.size(); ++i) {
+        CHECK(unit[i] == got[i]);
+        CHECK(windowed_exp(scalar_size, window, table, c * v[i]) == scaled[i]);
+    }
+    // get_window_table (multiexp.tcc:809-846) is built on the device: every entry j 2^(r w) g,
+    // the last row's tail zero -- checked against the group law on the CPU
+    const size_t in_window = 1ul << window;
+    const size_t outerc = (scalar_size + window - 1) / window;
+    const size_t last_in_window = 1ul << (scalar_size - (outerc - 1) * window);
+    CHECK(table.size() == outerc);
+    GroupT gouter = GroupT::one();
+    for (size_t outer = 0; outer < outerc && outer < table.size(); ++outer) {
+        CHECK(table[outer].size() == in_window);
+        GroupT ginner = GroupT::zero();
+        const size_t cur = outer == outerc - 1 ? last_in_window : in_window;
+        for (size_t inner = 0; inner < in_window; ++inner) {
+            CHECK(table[outer][inner] == (inner < cur ? ginner : GroupT::zero()));
+            ginner = ginner + gouter;
+        }
+        for (size_t i = 0; i < window; ++i) {
+            gouter = gouter + gouter;
+        }
+    }
+    // a table the caller changed afterwards is no longer the resident one: it is uploaded
+    window_table<GroupT> other = table;
+    other[0][1] = other[0][2];
+    const std::vector<GroupT> got2 = batch_exp(scalar_size, window, other, v);
+    for (size_t i = 0; i < n && i < got2.size(); ++i) {
+        CHECK(windowed_exp(scalar_size, window, other, v[i]) == got2[i]);
     }
 }
 
@@ -304,6 +335,7 @@ int main()
         printf("EXCEPTION %s\n", e.what());
         return 2;
     }
+    printf("engine contexts: %zu\n", b200msm_device_count());
     printf("dropin_test: %d checks, %d failures, %llu GPU kernel launches\n", g_checks, g_failures,
            (unsigned long long)b200msm_launch_count());
     return g_failures == 0 && b200msm_launch_count() > 0 ? 0 : 1;

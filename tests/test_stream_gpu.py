@@ -104,6 +104,19 @@ def test_stream_with_precompute_matches_reference(engine, ref, gid):
         for lo, hi in zip(cuts[:-1], cuts[1:]):
             st.push(data[lo * per * pb:hi * per * pb], hi - lo)
         np.testing.assert_array_equal(affine(engine, gid, st.finish()), plain, err_msg=f"c={c}")
+        # reference_carry: the reference's own recoding with the top carry dropped -- identical to
+        # what multi_exp_stream_with_precompute returns for EVERY c, including the dividing one
+        # where that differs from the true sum (field_utils.tcc:205-239)
+        streamed = ref.multi_exp_stream(gid, data, scalars, form=1, precompute_c=c)
+        if streamed is not None:
+            st = engine.MsmStream(gid, scalars, encoding=engine.STREAM_BINARY_MONTGOMERY,
+                                  precompute_c=c, reference_carry=True)
+            for lo, hi in zip(cuts[:-1], cuts[1:]):
+                st.push(data[lo * per * pb:hi * per * pb], hi - lo)
+            np.testing.assert_array_equal(affine(engine, gid, st.finish()), streamed,
+                                          err_msg=f"c={c} reference carry")
+            if c == DIVIDING_C[gid]:
+                assert not np.array_equal(streamed, plain), "edge scalars should lose their top carry"
 
 
 @pytest.mark.parametrize("gid", GROUPS)

@@ -20,9 +20,9 @@ def test_wire_msm_matches_reference(engine, ref, gid, n):
     pw, sw = ref.wire_group_write(gid, bases), ref.wire_scalar_write(gid, scalars)
     assert len(pw) == n * engine.wire_point_bytes(gid)
     want = ref.wire_group_write(gid, ref.multi_exp(gid, bases, scalars).reshape(1, -1))
-    for flags in (0, engine.WIRE_CHECK_CURVE, engine.WIRE_CHECK_CURVE | engine.WIRE_CHECK_SUBGROUP):
-        if flags & engine.WIRE_CHECK_SUBGROUP and n > 2:
-            continue  # n scalar multiplications; covered at small n
+    skip_both = engine.WIRE_SKIP_CURVE_CHECK | engine.WIRE_SKIP_SUBGROUP_CHECK
+    # default = both checks of group_element_read; then the opt-outs
+    for flags in (0, engine.WIRE_SKIP_SUBGROUP_CHECK, skip_both):
         assert engine.multi_exp_wire(gid, pw, sw, flags) == want
 
 
@@ -49,7 +49,7 @@ def test_wire_rejects_what_the_reference_rejects(engine, ref, gid):
     pw = bytearray(ref.wire_group_write(gid, P))
     sw = bytearray(ref.wire_scalar_write(gid, ref.gen_scalars(gid, 2)))
     cb = g.fq.nbytes
-    both = engine.WIRE_CHECK_CURVE | engine.WIRE_CHECK_SUBGROUP
+    skip_sub = engine.WIRE_SKIP_SUBGROUP_CHECK
     # coordinate >= modulus (ffi_serialization.tcc:64-75)
     bad = bytearray(pw)
     bad[-cb:] = g.fq.p.to_bytes(cb, "big")
@@ -67,7 +67,9 @@ def test_wire_rejects_what_the_reference_rejects(engine, ref, gid):
     off[-1] ^= 1
     assert not ref.wire_group_read(gid, bytes(off))[1].all()
     with pytest.raises(engine.B200MsmError, match="curve"):
-        engine.multi_exp_wire(gid, bytes(off), bytes(sw), engine.WIRE_CHECK_CURVE)
+        engine.multi_exp_wire(gid, bytes(off), bytes(sw))
+    with pytest.raises(engine.B200MsmError, match="curve"):
+        engine.multi_exp_wire(gid, bytes(off), bytes(sw), skip_sub)
     # on the curve but outside the prime-order subgroup (is_in_safe_subgroup); alt_bn128 G1 has
     # cofactor 1, so every curve point passes there
     if gid in (2, 3, 5, 6):  # prime coordinate field and cofactor > 1
@@ -81,9 +83,10 @@ def test_wire_rejects_what_the_reference_rejects(engine, ref, gid):
         stray = pm.wire_point(g, (x, y)) + bytes(pw[len(pw) // 2:])
         accepted = ref.wire_group_read(gid, stray)[1]
         assert not accepted[0] and accepted[1]
-        engine.multi_exp_wire(gid, stray, bytes(sw), engine.WIRE_CHECK_CURVE)  # on the curve: accepted
+        # rejected BY DEFAULT, as the reference's reader rejects it; accepted only on opt-out
         with pytest.raises(engine.B200MsmError, match="subgroup"):
-            engine.multi_exp_wire(gid, stray, bytes(sw), both)
+            engine.multi_exp_wire(gid, stray, bytes(sw))
+        engine.multi_exp_wire(gid, stray, bytes(sw), skip_sub)  # on the curve: accepted
     # sizes must match exactly
     with pytest.raises(engine.B200MsmError):
         engine.multi_exp_wire(gid, bytes(pw[:-1]), bytes(sw), 0)
