@@ -311,10 +311,13 @@ def group_sum(group: int, points) -> np.ndarray:
     return out
 
 
-def batch_to_special(group: int, points) -> np.ndarray:
-    """libff::batch_to_special<G>(vec): returns the normalised copy (the C ABI works in place)."""
+def batch_to_special(group: int, points, inplace: bool = False) -> np.ndarray:
+    """libff::batch_to_special<G>(vec): returns the normalised copy (the C ABI works in place, as
+    the reference does; `inplace=True` normalises the caller's own contiguous array)."""
     _ensure_init()
-    p = _as_u64(points, "points").copy()
+    p = _as_u64(points, "points")
+    if not inplace or p is not points:
+        p = p.copy()
     gb = group_bytes(group)
     n = _count(p, gb, "points")
     if not load().b200msm_batch_to_special(group, _ptr(p), p.nbytes, n):
@@ -345,22 +348,26 @@ def debug_op(group: int, op: int, a, b=None) -> np.ndarray:
     return out
 
 
-def batch_exp(group: int, scalar_size: int, window: int, table, scalars) -> np.ndarray:
+def batch_exp(group: int, scalar_size: int, window: int, table, scalars, out=None) -> np.ndarray:
     """libff::batch_exp<G, Fr>(scalar_size, window, table, v).  `table` is a sequence of rows
     (window_table<G> = vector<vector<G>>), a (rows, 1 << window, words) array, or a resident
     WindowTable."""
-    return batch_exp_with_coeff(group, scalar_size, window, table, None, scalars)
+    return batch_exp_with_coeff(group, scalar_size, window, table, None, scalars, out)
 
 
 def batch_exp_with_coeff(group: int, scalar_size: int, window: int, table, coeff,
-                         scalars) -> np.ndarray:
+                         scalars, out=None) -> np.ndarray:
     """libff::batch_exp_with_coeff<G, Fr>(scalar_size, window, table, coeff, v) (multiexp.tcc:
-    917-947): out[i] = (coeff * v[i]) g.  coeff: one Fr element (Montgomery limbs) or None."""
+    917-947): out[i] = (coeff * v[i]) g.  coeff: one Fr element (Montgomery limbs) or None.
+    `out`: a caller-owned (n, words) uint64 array to write into (else a new one)."""
     _ensure_init()
     gb, sb = group_bytes(group), scalar_bytes(group)
     s = _as_u64(scalars, "scalars")
     n = _count(s, sb, "scalars")
-    out = np.zeros((n, gb // 8), dtype=np.uint64)
+    if out is None:
+        out = np.zeros((n, gb // 8), dtype=np.uint64)
+    elif out.dtype != np.uint64 or not out.flags.c_contiguous or out.nbytes != n * gb:
+        raise B200MsmError("batch_exp: `out` must be a contiguous uint64 array of n elements")
     cf = None if coeff is None else _as_u64(coeff, "coeff").reshape(-1)
     cp, cb = (None, 0) if cf is None else (_ptr(cf), cf.nbytes)
     if isinstance(table, WindowTable):

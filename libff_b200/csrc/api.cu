@@ -73,26 +73,25 @@ void Ctx::release_all() {
     }
 }
 
-bool Stager::init() {
-    if (ready) return true;
-    for (int l = 0; l < STAGE_LANES; l++)
+bool Stager::init(int want_lanes) {
+    want_lanes = std::min(std::max(want_lanes, 1), STAGE_LANES_MAX);
+    for (; lanes < want_lanes; lanes++)
         for (int b = 0; b < 2; b++) {
-            B200_CUDA(cudaHostAlloc(&buf[l][b], STAGE_BYTES, cudaHostAllocDefault));
-            B200_CUDA(cudaEventCreateWithFlags(&ev[l][b], cudaEventDisableTiming));
+            B200_CUDA(cudaHostAlloc(&buf[lanes][b], STAGE_BYTES, cudaHostAllocDefault));
+            B200_CUDA(cudaEventCreateWithFlags(&ev[lanes][b], cudaEventDisableTiming));
         }
-    ready = true;
     return true;
 }
 
 void Stager::release() {
-    for (int l = 0; l < STAGE_LANES; l++)
+    for (int l = 0; l < STAGE_LANES_MAX; l++)
         for (int b = 0; b < 2; b++) {
             if (buf[l][b]) cudaFreeHost(buf[l][b]);
             if (ev[l][b]) cudaEventDestroy(ev[l][b]);
             buf[l][b] = nullptr;
             ev[l][b] = nullptr;
         }
-    ready = false;
+    lanes = 0;
 }
 
 namespace {
@@ -254,7 +253,11 @@ bool run_msm(Ctx &ctx, const GroupOps *ops, const void *d_aff, const uint8_t *d_
 
 // How many point ranges a host-buffer multi_exp is cut into so that the upload of range k + 1
 // overlaps the computation of range k.
-size_t pick_parts(const Ctx &ctx, size_t n) {
+size_t pick_parts(const Ctx &ctx, size_t n, bool scalars_only) {
+    if (scalars_only && ctx.opt_h2d_parts == 0) {
+        // a quarter of the bytes: few ranges, so that the buckets stay dense in every range
+        return n < ((size_t)1 << 21) ? 1 : 4;
+    }
     if (ctx.opt_h2d_parts > 0) return std::min<size_t>((size_t)ctx.opt_h2d_parts, std::max<size_t>(n, 1));
     if (n < ((size_t)1 << 21)) return 1;
     if (n < ((size_t)1 << 22)) return 2;
@@ -267,8 +270,9 @@ size_t pick_parts(const Ctx &ctx, size_t n) {
 // Range boundaries of a pipelined call: sizes grow geometrically (x h2d_growth %, default 1.3),
 // so the first upload -- the only one nothing overlaps -- is short, while the later, longer MSMs
 // still finish after their successor's upload.  bounds has parts + 1 entries.
-void pick_bounds(const Ctx &ctx, size_t n, size_t parts, size_t *bounds) {
+void pick_bounds(const Ctx &ctx, size_t n, size_t parts, size_t *bounds, bool scalars_only) {
     const double g = ctx.opt_h2d_growth > 0 ? ctx.opt_h2d_growth / 100.0
+                     : scalars_only ? 2.0
                      : (ctx.opt_h2d_shared_buckets && parts > 5) ? 1.2 : 1.3;
     double total = 0, w = 1;
     for (size_t k = 0; k < parts; k++, w *= g) total += w;
@@ -309,16 +313,17 @@ bool upload(Ctx &ctx, void *dst, const void *src, size_t count, size_t stride, s
     const size_t bytes = count * stride;
     if (!pack && (is_pinned(src) || bytes < STAGE_BYTES))
         return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, cs) == cudaSuccess;
-    if (!ctx.stager.init()) return false;
     const size_t per = std::max<size_t>(1, STAGE_BYTES / keep);  // records per slice
     const size_t slices = (count + per - 1) / per;
+    const int LANES = (int)std::min<size_t>((size_t)std::min(std::max(ctx.opt_stage_lanes, 1), STAGE_LANES_MAX), slices);
+    if (!ctx.stager.init(LANES)) return false;
     std::atomic<bool> ok{true};
     Stager &sg = ctx.stager;
     const int device = ctx.device;
     auto lane_fn = [&](int l) {
         if (cudaSetDevice(device) != cudaSuccess) ok = false;
         int b = 0;
-        for (size_t s = l; s < slices && ok; s += STAGE_LANES, b ^= 1) {
+        for (size_t s = l; s < slices && ok; s += LANES, b ^= 1) {
             const size_t r0 = s * per, rn = std::min(per, count - r0);
             // the previous DMA out of this buffer must have finished
             if (cudaEventSynchronize(sg.ev[l][b]) != cudaSuccess) ok = false;
@@ -347,13 +352,63 @@ bool upload(Ctx &ctx, void *dst, const void *src, size_t count, size_t stride, s
                 ok = false;
         }
     };
-    if (slices == 1) {
+    if (LANES == 1) {
         lane_fn(0);
         return ok;
     }
-    std::thread lanes[STAGE_LANES];
-    for (int l = 0; l < STAGE_LANES; l++) lanes[l] = std::thread(lane_fn, l);
+    std::vector<std::thread> lanes;
+    for (int l = 0; l < LANES; l++) lanes.emplace_back(lane_fn, l);
     for (auto &t : lanes) t.join();
+    return ok;
+}
+
+// Device -> host copy of a large result array (batch_exp, batch_to_special).  Pageable
+// destinations -- a std::vector<G> -- go through the pinned ring as the uploads do: the DMA of
+// slice s + LANES runs while slice s is copied out of its staging buffer.  Synchronous: the data
+// is in `dst` on return.
+bool download(Ctx &ctx, void *dst, const void *src, size_t bytes, cudaStream_t cs) {
+    if (bytes == 0) return true;
+    if (is_pinned(dst) || bytes < 2 * STAGE_BYTES) {
+        B200_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, cs));
+        B200_CUDA(cudaStreamSynchronize(cs));
+        return true;
+    }
+    const size_t slices = (bytes + STAGE_BYTES - 1) / STAGE_BYTES;
+    const int LANES = (int)std::min<size_t>((size_t)std::min(std::max(ctx.opt_stage_lanes, 1), STAGE_LANES_MAX), slices);
+    if (!ctx.stager.init(LANES)) return false;
+    B200_CUDA(cudaStreamSynchronize(cs));  // the producer kernels are done: lanes copy on their own streams
+    std::atomic<bool> ok{true};
+    Stager &sg = ctx.stager;
+    const int device = ctx.device;
+    auto lane_fn = [&](int l) {
+        cudaStream_t ls = nullptr;
+        if (cudaSetDevice(device) != cudaSuccess ||
+            cudaStreamCreateWithFlags(&ls, cudaStreamNonBlocking) != cudaSuccess) {
+            ok = false;
+            return;
+        }
+        auto issue = [&](size_t s, int b) {
+            const size_t off = s * STAGE_BYTES, len = std::min(STAGE_BYTES, bytes - off);
+            if (cudaMemcpyAsync(sg.buf[l][b], (const char *)src + off, len, cudaMemcpyDeviceToHost, ls) !=
+                    cudaSuccess ||
+                cudaEventRecord(sg.ev[l][b], ls) != cudaSuccess)
+                ok = false;
+        };
+        int b = 0;
+        if ((size_t)l < slices) issue((size_t)l, 0);
+        for (size_t s = l; s < slices && ok; s += LANES, b ^= 1) {
+            if (s + LANES < slices) issue(s + LANES, b ^ 1);
+            if (cudaEventSynchronize(sg.ev[l][b]) != cudaSuccess) ok = false;
+            const size_t off = s * STAGE_BYTES, len = std::min(STAGE_BYTES, bytes - off);
+            memcpy((char *)dst + off, sg.buf[l][b], len);
+        }
+        cudaStreamSynchronize(ls);
+        cudaStreamDestroy(ls);
+    };
+    std::vector<std::thread> lanes;
+    for (int l = 0; l < LANES; l++) lanes.emplace_back(lane_fn, l);
+    for (auto &t : lanes) t.join();
+    if (!ok) set_error("device to host copy failed");
     return ok;
 }
 
@@ -422,10 +477,10 @@ bool msm_host_on(Ctx &ctx, const GroupOps *ops, const void *bases, const void *d
     }
     if (!ctx.reserve(SL_SCALARS, n * sb, &d_sc)) return false;
     if (!ctx.reserve(SL_OUT, gb, &d_out)) return false;
-    size_t parts = pick_parts(ctx, n);
+    size_t parts = pick_parts(ctx, n, resident);
     size_t bounds[MAX_H2D_PARTS + 1] = {0};
     if (parts > 1) {  // ranges that came out empty (tiny n) are dropped
-        pick_bounds(ctx, n, parts, bounds);
+        pick_bounds(ctx, n, parts, bounds, resident);
         size_t m = 0;
         for (size_t k = 0; k < parts; k++)
             if (bounds[k + 1] > bounds[k]) bounds[++m] = bounds[k + 1];
@@ -449,7 +504,6 @@ bool msm_host_on(Ctx &ctx, const GroupOps *ops, const void *bases, const void *d
     // still in flight: the copy stream starts after everything queued so far
     B200_CUDA(cudaEventRecord(ctx.ev_sync, ctx.stream));
     B200_CUDA(cudaStreamWaitEvent(ctx.copy_stream, ctx.ev_sync, 0));
-    if (!ctx.stager.init()) return false;
     Uploader up;
     cudaStream_t cs = ctx.copy_stream;
     cudaEvent_t *evs = ctx.ev_copy;
@@ -501,15 +555,27 @@ bool msm_host_on(Ctx &ctx, const GroupOps *ops, const void *bases, const void *d
         ctx.range_last = k + 1 == parts;
         up.wait_for((int)k);
         if (up.failed) return set_error("multi_exp: host to device copy failed"), false;
-        B200_CUDA(cudaStreamWaitEvent(ctx.stream, ctx.ev_copy[k], 0));
-        if (!resident &&
-            !ops->ingest(ctx, (char *)d_raw + lo * rb, cnt, form, (char *)d_aff + lo * ab,
-                         (uint8_t *)d_inf + lo))
-            return false;
-        B200_CUDA(cudaEventRecord(ctx.ev[PH_INGEST + 1], ctx.stream));
-        if (!ops->msm(ctx, (char *)d_aff + lo * ab, (const uint8_t *)d_inf + lo, (char *)d_sc + lo * sb,
-                      cnt, (char *)d_parts + k * gb, nullptr))
-            return false;
+        // The range's ingest and counting sort run on the sort stream, ordered only behind the
+        // range's own upload: they overlap the accumulation of range k - 1 on the main stream.
+        B200_CUDA(cudaStreamWaitEvent(ctx.sort_stream, ctx.ev_copy[k], 0));
+        {
+            struct StreamSwap {  // the ingest kernels are issued on Ctx::stream
+                Ctx &c;
+                cudaStream_t keep;
+                explicit StreamSwap(Ctx &c_) : c(c_), keep(c_.stream) { c.stream = c.sort_stream; }
+                ~StreamSwap() { c.stream = keep; }
+            } swap(ctx);
+            if (!resident &&
+                !ops->ingest(ctx, (char *)d_raw + lo * rb, cnt, form, (char *)d_aff + lo * ab,
+                             (uint8_t *)d_inf + lo))
+                return false;
+        }
+        B200_CUDA(cudaEventRecord(ctx.ev[PH_INGEST + 1], ctx.sort_stream));
+        ctx.sort_inputs_ready = true;
+        const bool msm_ok = ops->msm(ctx, (char *)d_aff + lo * ab, (const uint8_t *)d_inf + lo,
+                                     (char *)d_sc + lo * sb, cnt, (char *)d_parts + k * gb, nullptr);
+        ctx.sort_inputs_ready = false;
+        if (!msm_ok) return false;
         if (ctx.opt_trace) {  // development aid: per-range phase times (serialises the pipeline)
             B200_CUDA(cudaDeviceSynchronize());
             fprintf(stderr, "[b200msm] device %d range %zu: %zu points", ctx.device, k, cnt);
@@ -610,7 +676,9 @@ Ctx *make_ctx(int device, int index) {
     if (!ok(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi))) return nullptr;
     if (!ok(cudaStreamCreateWithPriority(&ctx->tail_stream, cudaStreamNonBlocking, prio_hi))) return nullptr;
     if (!ok(cudaStreamCreateWithFlags(&ctx->acc_stream, cudaStreamNonBlocking))) return nullptr;
-    if (!ok(cudaStreamCreateWithFlags(&ctx->sort_stream, cudaStreamNonBlocking))) return nullptr;
+    // high priority: the accumulation kernels fill every SM, and the sort's short blocks must get
+    // the slots their blocks free instead of waiting for the last wave
+    if (!ok(cudaStreamCreateWithPriority(&ctx->sort_stream, cudaStreamNonBlocking, prio_hi))) return nullptr;
     if (!ok(cudaEventCreateWithFlags(&ctx->ev_group_go, cudaEventDisableTiming))) return nullptr;
     for (auto &e : ctx->ev_group)
         if (!ok(cudaEventCreateWithFlags(&e, cudaEventDisableTiming))) return nullptr;
@@ -620,6 +688,7 @@ Ctx *make_ctx(int device, int index) {
         if (!ok(cudaEventCreate(&e))) return nullptr;
     if (!ok(cudaEventCreateWithFlags(&ctx->ev_tail_go, cudaEventDisableTiming))) return nullptr;
     if (!ok(cudaEventCreateWithFlags(&ctx->ev_tail_done, cudaEventDisableTiming))) return nullptr;
+    if (!ok(cudaHostAlloc((void **)&ctx->host_meta, 64, cudaHostAllocDefault))) return nullptr;
     return ctx.release();
 }
 
@@ -628,6 +697,8 @@ void destroy_ctx(Ctx *c) {
     cudaDeviceSynchronize();
     c->release_all();
     c->stager.release();
+    if (c->host_meta) cudaFreeHost(c->host_meta);
+    c->host_meta = nullptr;
     for (auto &e : c->ev) cudaEventDestroy(e);
     for (auto &e : c->ev_copy) cudaEventDestroy(e);
     cudaEventDestroy(c->ev_sync);
@@ -1310,10 +1381,7 @@ bool b200msm_batch_to_special(uint32_t group, void *inout, size_t bytes, size_t 
     return fan_out(sp.D, [&](size_t k) {
         Ctx &ctx = *g_ctxs[k];
         if (!bind(ctx)) return false;
-        B200_CUDA(cudaMemcpyAsync((char *)inout + sp.lo(k) * gb, d_done[k], sp.count(k) * gb,
-                                  cudaMemcpyDeviceToHost, ctx.stream));
-        B200_CUDA(cudaStreamSynchronize(ctx.stream));
-        return true;
+        return download(ctx, (char *)inout + sp.lo(k) * gb, d_done[k], sp.count(k) * gb, ctx.stream);
     });
 }
 
@@ -1360,10 +1428,7 @@ bool batch_exp_from(const GroupOps *ops, const Resident &rt, const void *scalars
     return fan_out(sp.D, [&](size_t k) {
         Ctx &ctx = *g_ctxs[rt.shards[k].ci];
         if (!bind(ctx)) return false;
-        B200_CUDA(cudaMemcpyAsync((char *)out + sp.lo(k) * gb, d_done[k], sp.count(k) * gb,
-                                  cudaMemcpyDeviceToHost, ctx.stream));
-        B200_CUDA(cudaStreamSynchronize(ctx.stream));
-        return true;
+        return download(ctx, (char *)out + sp.lo(k) * gb, d_done[k], sp.count(k) * gb, ctx.stream);
     });
 }
 
@@ -1578,6 +1643,7 @@ bool b200msm_set_option(const char *name, int64_t value) {
         {"h2d_shared_buckets", &Ctx::opt_h2d_shared_buckets, 0, 1},
         {"h2d_parts", &Ctx::opt_h2d_parts, 0, MAX_H2D_PARTS},
         {"h2d_pack", &Ctx::opt_h2d_pack, 0, 2},
+        {"stage_lanes", &Ctx::opt_stage_lanes, 1, STAGE_LANES_MAX},
         {"sort_overlap", &Ctx::opt_sort_overlap, 0, 64},
         {"coop_accum", &Ctx::opt_coop_accum, 0, 2},
     };

@@ -92,13 +92,13 @@ constexpr int MAX_H2D_PARTS = 16;
 // Pinned staging ring of one engine context.  Pageable sources -- what a std::vector<G> of a libff
 // caller is -- would be staged by the driver at ~10 GB/s; instead STAGE_LANES host threads copy
 // slices into these buffers and issue the DMA from there, which keeps the PCIe link busy.
-constexpr int STAGE_LANES = 4;
+constexpr int STAGE_LANES_MAX = 16;
 constexpr size_t STAGE_BYTES = (size_t)8 << 20;
 struct Stager {
-    void *buf[STAGE_LANES][2] = {};
-    cudaEvent_t ev[STAGE_LANES][2] = {};
-    bool ready = false;
-    bool init();
+    void *buf[STAGE_LANES_MAX][2] = {};
+    cudaEvent_t ev[STAGE_LANES_MAX][2] = {};
+    int lanes = 0;  // lanes whose buffers exist
+    bool init(int want_lanes);
     void release();
 };
 
@@ -128,6 +128,7 @@ struct Ctx {
     cudaStream_t sort_stream = nullptr;
     cudaEvent_t ev_sort[4] = {};  // [p]: sort into buffer set p done; [2 + p]: its reader done
     int sort_parity = 0;          // buffer set the next sort writes
+    uint32_t *host_meta = nullptr;   // pinned: item counts read back between the halves of a sort
     bool sort_inputs_ready = false;  // the caller queued the inputs' upload / ingest on sort_stream
     bool defer_tail = false;    // set by the pipelined caller
     // Point ranges of ONE host-buffer call that share a bucket set (set by the pipelined caller):
@@ -153,6 +154,7 @@ struct Ctx {
     int opt_carry_segment = 0; // carries per thread in the later accumulation rounds; 0 = automatic
     int opt_reduce_chunk = 0; // log2 of the buckets per thread in the reduction; 0 = automatic
     int opt_h2d_pack = 1;     // special-form bases leave Z behind on upload: 0 never, 1 pageable sources, 2 always
+    int opt_stage_lanes = 8;  // host threads that stage pageable buffers through the pinned ring
     int opt_sort_overlap = 0; // window groups whose sort overlaps the previous accumulation; 0 = automatic
     int opt_coop_accum = 0;   // lane-cooperative accumulation of the wide fields: 0 automatic, 1 off, 2 on
 

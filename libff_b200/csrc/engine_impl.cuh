@@ -195,6 +195,9 @@ MsmGeom<C> msm_geom(const Ctx &ctx, size_t n, const MsmShape *shape) {
     return g;
 }
 
+#ifndef B200_SORT_OVERLAP_MIN_LOG2
+#define B200_SORT_OVERLAP_MIN_LOG2 24
+#endif
 // Groups of windows (ascending).  The counting sort of group g + 1 -- digit pass, scan, scatter:
 // L2-atomic / random-access bound -- runs on the sort stream under the accumulation of group g,
 // which is bound by the integer multiply pipe: different resources, so the 10 % of the step the
@@ -203,10 +206,13 @@ MsmGeom<C> msm_geom(const Ctx &ctx, size_t n, const MsmShape *shape) {
 inline std::vector<int> pick_sort_groups(const Ctx &ctx, size_t n, int W, bool single) {
     std::vector<int> sizes;
     int want = ctx.opt_sort_overlap ? ctx.opt_sort_overlap : ctx.opt_window_groups;
-    if (single || W <= 2 || want == 1) return {W};
+    if (single || W <= 3 || want == 1) return {W};
     if (want == 0) {
-        if ((uint64_t)n * W < (1ull << 23)) return {W};  // small inputs: launch overheads dominate
-        want = (W + 2) / 3 + 1;
+        if ((uint64_t)n * W < (1ull << B200_SORT_OVERLAP_MIN_LOG2)) return {W};  // launch overheads dominate
+        // Sorting a window costs ~13 % of accumulating it, so a group may be several times larger
+        // than the one whose accumulation hides its sort: 1, 4, the rest.
+        if (W <= 6) return {1, W - 1};
+        return {1, 4, W - 5};
     }
     want = std::min(want, W);
     sizes.push_back(1);
@@ -358,8 +364,11 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
     // p done", ev_sort[2 + p] = "the accumulation that read set p is done".
     cudaStream_t ss = ctx.sort_stream;
     B200_CUDA(cudaEventRecord(ctx.ev_group_go, st));
-    if (!ctx.sort_inputs_ready)  // inputs (uploads, ingest) were queued on the main stream
-        B200_CUDA(cudaStreamWaitEvent(ss, ctx.ev_group_go, 0));
+    // inputs (uploads, ingest) were queued on the main stream -- or, for the ranges of a pipelined
+    // host call that share one bucket set, on the sort stream: their sort then starts under the
+    // previous range's accumulation (an independent MSM per range may not: its digit pass
+    // rewrites the histogram the previous range's bucket reduction still reads)
+    if (!(ctx.sort_inputs_ready && ranged)) B200_CUDA(cudaStreamWaitEvent(ss, ctx.ev_group_go, 0));
     if (range_first) B200_CUDA(cudaMemsetAsync(used_windows, 0, 4, ss));
     if (ranged && range_first) B200_CUDA(cudaMemsetAsync(sc.live, 0, M * 4, ss));
 
@@ -368,6 +377,7 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
     size_t toff = 0;      // carry entries written so far (all groups share one carry list)
     int w_lo = 0;
     int Wu = W;           // windows that hold items (known after the first digit pass)
+    size_t call_items = 0;  // estimate of the sorted items of all groups
     bool any_items = false;
     cudaStream_t last_as = st;
     // sort of group g: queued on the sort stream; returns the group's item count (host sync)
@@ -377,11 +387,11 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
         size_t t1;
         int lo, hi;
     };
-    auto sort_group = [&](int lo, int hi, bool first, Sorted &out) -> bool {
+    // First half: histogram, digits, scan and the read-back of the item count, all queued.
+    auto sort_begin = [&](int lo, int hi, bool first, Sorted &out) -> bool {
         const int p = ctx.sort_parity;
         ctx.sort_parity ^= 1;
-        const int wg = hi - lo;
-        const size_t mg = pre ? M : (size_t)wg * B;
+        const size_t mg = pre ? M : (size_t)(hi - lo) * B;
         uint32_t *hist_g = sc.hist + (pre ? 0 : (size_t)lo * B);
         // (consecutive groups use different buffer sets, so the item count a scan writes behind
         // its slice never lands in a neighbour's)
@@ -404,18 +414,34 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
         k_scan_apply<<<tiles, SCAN_THREADS, 0, ss>>>(hist_g, sc.tile_sums, tiles, off_g, (uint32_t)mg);
         B200_LAUNCH_CHECK(ctx);
         if (first) B200_CUDA(cudaEventRecord(ctx.ev[PH_SCAN + 1], ss));
-        // the number of sorted items sizes the accumulation segments
-        uint32_t meta[2] = {0, 0};
-        B200_CUDA(cudaMemcpyAsync(&meta[0], off_g + mg, 4, cudaMemcpyDeviceToHost, ss));
-        B200_CUDA(cudaMemcpyAsync(&meta[1], used_windows, 4, cudaMemcpyDeviceToHost, ss));
-        B200_CUDA(cudaStreamSynchronize(ss));
+        // the number of sorted items sizes the accumulation segments (pinned destination: the
+        // copies are queued, the host waits for them in sort_finish)
+        B200_CUDA(cudaMemcpyAsync(&ctx.host_meta[2 * p], off_g + mg, 4, cudaMemcpyDeviceToHost, ss));
+        B200_CUDA(cudaMemcpyAsync(&ctx.host_meta[2 * p + 1], used_windows, 4, cudaMemcpyDeviceToHost, ss));
         out.p = p, out.lo = lo, out.hi = hi;
-        out.total = meta[0];
-        if (first) Wu = pre ? 1 : std::max<int>(1, std::min<int>(W, (int)meta[1]));
-        // segment length from the parallelism the whole call offers (groups overlap pairwise)
-        const size_t est = G > 1 ? (size_t)out.total * 2 : (size_t)out.total;
-        out.seg = pick_segment<C>(ctx, est);
+        return true;
+    };
+    // Second half: the host learns the item count, then the scatter is queued.
+    auto sort_finish = [&](bool first, Sorted &out) -> bool {
+        const int p = out.p;
+        const int wg = out.hi - out.lo;
+        uint32_t *off_g = sc.offsets[p] + (pre ? 0 : (size_t)out.lo * B);
+        B200_CUDA(cudaStreamSynchronize(ss));
+        out.total = ctx.host_meta[2 * p];
+        if (first) Wu = pre ? 1 : std::max<int>(1, std::min<int>(W, (int)ctx.host_meta[2 * p + 1]));
+        // One segment length for the whole call, the one a single sort of all windows would get
+        // (estimated from the first group, a single window): short segments in the small early
+        // groups would only multiply the carries, and those groups run beside the next sort anyway.
+        if (first) call_items = G > 1 ? (size_t)out.total * (size_t)W / (size_t)(out.hi - out.lo) : (size_t)out.total;
+        out.seg = pick_segment<C>(ctx, std::max(call_items, (size_t)out.total));
         out.t1 = ((size_t)out.total + out.seg - 1) / out.seg;
+        // (an estimate far below this group's own load -- a sparse first window -- must not
+        // overrun the carry entries reserved for the group)
+        const size_t room = segments_bound<C>(ctx, (size_t)wg * n) - 2;
+        while (out.t1 > room) {
+            out.seg *= 2;
+            out.t1 = ((size_t)out.total + out.seg - 1) / out.seg;
+        }
         if (out.total > 0) {
             k_scatter<C><<<dim3(cdiv(n, 256), wg), 256, 0, ss>>>(
                 sc.digits[p], sc.ranks[p], off_g, sc.sorted[p], sc.seg_bucket[p], (uint32_t)n, out.seg,
@@ -461,9 +487,10 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
         B200_CUDA(cudaStreamWaitEvent(st, ctx.ev_tail_done, 0));
         ctx.tail_pending = false;
     }
-    // group 0 is sorted up front; from then on: sort g + 1 is queued, then accumulation g
+    // group 0 is sorted up front; from then on the first half of sort g + 1 is queued, then
+    // accumulation g is launched, and only then the host waits for the item count of g + 1
     Sorted cur, nxt;
-    if (!sort_group(0, gsizes[0], true, cur)) return false;
+    if (!sort_begin(0, gsizes[0], true, cur) || !sort_finish(true, cur)) return false;
     if (ctx.tail_pending) {  // ranged: the previous range's carry rounds add into the same buckets
         B200_CUDA(cudaStreamWaitEvent(st, ctx.ev_tail_done, 0));
         ctx.tail_pending = false;
@@ -473,12 +500,13 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
         bool have_next = false;
         if (g + 1 < G && w_lo < Wu) {  // windows from Wu up hold no items
             const int hi = std::min(w_lo + gsizes[g + 1], Wu);
-            if (!sort_group(w_lo, hi, false, nxt)) return false;
+            if (!sort_begin(w_lo, hi, false, nxt)) return false;
             w_lo = hi;
             have_next = true;
         }
         if (!accumulate_group(cur, g)) return false;
         if (!have_next) break;
+        if (!sort_finish(false, nxt)) return false;
         cur = nxt;
     }
     if (last_as != st) {  // the main stream continues after the last accumulation
