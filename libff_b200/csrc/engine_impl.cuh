@@ -165,6 +165,24 @@ inline uint32_t pick_segment(const Ctx &ctx, size_t total) {
     return seg;
 }
 
+// the shared-memory accumulation kernel exists for the wide prime fields only
+template <class C>
+bool attr_accum_sm() {
+    if constexpr (SmemAccum<C>::value)
+        B200_CUDA(cudaFuncSetAttribute(k_accum_first_sm<C>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)SmemAccum<C>::BYTES));
+    return true;
+}
+template <class C, class... A>
+void launch_accum_sm(unsigned blocks, cudaStream_t st, const Entry *sorted, const uint32_t *offsets,
+                     const uint32_t *seg_bucket, uint32_t total, uint32_t seg, uint32_t t1,
+                     const uint32_t *aff, uint32_t *buckets, uint32_t *carry_key, uint32_t *carry_pt,
+                     uint32_t key_base) {
+    if constexpr (SmemAccum<C>::value)
+        k_accum_first_sm<C><<<blocks, SmemAccum<C>::THREADS, SmemAccum<C>::BYTES, st>>>(
+            sorted, offsets, seg_bucket, total, seg, 0u, t1, aff, buckets, carry_key, carry_pt, key_base);
+}
+
 // ------------------------------------------------------------------------------------------
 // Geometry of one MSM call
 template <class C>
@@ -355,8 +373,11 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
     if (!(ctx.attr_mask & (1u << C::ID))) {  // function attributes are per device
         B200_CUDA(cudaFuncSetAttribute(k_window_reduce<C, WR_THREADS>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wr_smem));
+        if (!attr_accum_sm<C>()) return false;
         ctx.attr_mask |= 1u << C::ID;
     }
+    // wide prime fields: the accumulator lives in shared memory (option coop_accum = 1 turns it off)
+    const bool use_smem_accum = SmemAccum<C>::value && ctx.opt_coop_accum != 1;
 
     // --- stream choreography.  Sorts run on the sort stream, accumulations alternate between the
     // main and the second accumulation stream (the partly filled last wave of one launch overlaps
@@ -472,6 +493,11 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
                 k_accum_first_merge<C><<<cdiv(sg.t1, 128), 128, 0, as>>>(
                     sc.sorted[sg.p], off_g, sc.seg_bucket[sg.p], sg.total, sg.seg, 0u, (uint32_t)sg.t1,
                     (const uint32_t *)d_aff, bk, sc.keyA + toff, sc.ptA + toff * R::XW, key_base, sc.live);
+            else if (use_smem_accum)
+                launch_accum_sm<C>(cdiv(sg.t1, SmemAccum<C>::THREADS), as, sc.sorted[sg.p], off_g,
+                                   sc.seg_bucket[sg.p], sg.total, sg.seg, (uint32_t)sg.t1,
+                                   (const uint32_t *)d_aff, bk, sc.keyA + toff, sc.ptA + toff * R::XW,
+                                   key_base);
             else
                 k_accum_first<C><<<cdiv(sg.t1, 128), 128, 0, as>>>(
                     sc.sorted[sg.p], off_g, sc.seg_bucket[sg.p], sg.total, sg.seg, 0u, (uint32_t)sg.t1,

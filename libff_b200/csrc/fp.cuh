@@ -427,6 +427,60 @@ struct Fp {
         return finish(E, O);
     }
 
+    // ---- products whose second operand streams from shared memory ---------------------------
+    // Limb k of the streamed operand lies at sb[k * stride] (word-interleaved per-thread slots:
+    // conflict-free).  Only `a`, the two accumulators and one limb of b are in registers -- the
+    // register-resident product also holds all of b (and rotates it to keep its indices static).
+    // Row pairs in a loop, first pair peeled, as mul_rolled.
+    B200_DEV static Fp mul_sb_inline(const Fp &a, const uint32_t *sb, int stride) {
+        uint32_t E[N], O[N];
+        uint32_t b0 = sb[0], b1 = sb[stride];
+        uint32_t n0 = sb[2 * (size_t)stride], n1 = sb[3 * (size_t)stride];  // one row pair ahead
+        mont_row(E, O, a.v, b0, true);
+        mont_row(O, E, a.v, b1, false);
+#pragma unroll 1
+        for (int it = 1; it < N / 2; it++) {
+            b0 = n0, b1 = n1;
+            if (it + 1 < N / 2) {
+                const uint32_t *q = sb + (size_t)(2 * it + 2) * stride;
+                n0 = q[0], n1 = q[stride];
+            }
+            mont_row(E, O, a.v, b0, false);
+            mont_row(O, E, a.v, b1, false);
+        }
+        return finish(E, O);
+    }
+    B200_DEV static Fp mul_sb(const Fp &a, const uint32_t *sb, int stride) {
+        return mul_sb_inline(a, sb, stride);
+    }
+    // a * b + c * d with one reduction (see mul2), b and d streamed
+    B200_DEV static Fp mul2_sb(const Fp &a, const uint32_t *sb, const Fp &c, const uint32_t *sd,
+                               int stride) {
+        static_assert(SPARE2, "shared-reduction product needs two spare bits");
+        uint32_t E[N], O[N];
+        mont_row2(E, O, a.v, sb[0], c.v, sd[0], true);
+        mont_row2(O, E, a.v, sb[stride], c.v, sd[stride], false);
+#pragma unroll 1
+        for (int it = 1; it < N / 2; it++) {
+            const uint32_t *q = sb + (size_t)(2 * it) * stride, *r = sd + (size_t)(2 * it) * stride;
+            mont_row2(E, O, a.v, q[0], c.v, r[0], false);
+            mont_row2(O, E, a.v, q[stride], c.v, r[stride], false);
+        }
+        return finish(E, O);
+    }
+    // rows [0, N) of a product whose accumulators E, O the caller owns: lets a fused routine start
+    // the next product's first row without re-materialising anything
+    B200_DEV static Fp lds(const uint32_t *s, int stride) {
+        Fp r;
+#pragma unroll
+        for (int i = 0; i < N; i++) r.v[i] = s[(size_t)i * stride];
+        return r;
+    }
+    B200_DEV void sts(uint32_t *s, int stride) const {
+#pragma unroll
+        for (int i = 0; i < N; i++) s[(size_t)i * stride] = v[i];
+    }
+
     // The same product on the FP64 pipe (fp_dfma.cuh): identical canonical result, different
     // execution unit -- call sites split their independent products between mul and mul_d.
     B200_DEV static Fp mul_d(const Fp &a, const Fp &b) {

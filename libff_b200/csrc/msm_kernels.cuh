@@ -376,6 +376,264 @@ __global__ void __launch_bounds__(128, Raw<C>::XW <= 32 ? 4 : 1)
                               bucket_acc, carry_key, carry_pt, key_base, live);
 }
 
+// ------------------------------------------------------------------------------------------
+// First accumulation round of the WIDE prime fields (24 limbs: bw6_761) with the accumulator in
+// SHARED MEMORY.  One thread per segment as above, but a 24-limb XYZZ accumulator (96 words), the
+// point being added (48) and the temporaries of a mixed addition do not fit 255 registers: the
+// register-resident kernel spills (628 bytes of spill stores per thread, 8 warps per SM, 63 % of
+// the multiply pipe).  Here every thread owns six word-interleaved slots of shared memory
+// (X, Y, ZZ, ZZZ and two temporaries; limb k of slot e at smem[(e N + k) blockDim + tid]: no bank
+// conflicts) and every product streams its second operand from there one limb per row
+// (Fp::mul_sb): a product keeps only its first operand and the two accumulators in registers.
+// The next point is pulled towards the SM with an L2 prefetch instead of an early register load.
+#ifndef B200_SM_THREADS
+#define B200_SM_THREADS 64
+#endif
+#ifndef B200_SM_MINBLOCKS
+#define B200_SM_MINBLOCKS 4
+#endif
+template <class C>
+struct SmemAccum {
+    static constexpr bool value = !BaseLimbs<typename C::Fq>::EXT && BaseLimbs<typename C::Fq>::N >= 24;
+    static constexpr int SLOTS = 8;
+    static constexpr int THREADS = B200_SM_THREADS;
+    static constexpr size_t BYTES = (size_t)SLOTS * BaseLimbs<typename C::Fq>::N * THREADS * 4;
+};
+
+// The accumulator and the temporaries of a mixed addition in word-interleaved shared-memory slots;
+// the arithmetic is a short program of slot-to-slot operations, and every product of it runs
+// through ONE out-of-line routine (uprod).  Measured on the way here (profiles/sm_accum_r02.md):
+// a 24-limb row loop inlined at every product is 60-140 KB of code and the kernel starves on
+// instruction fetch (sm__icc hit rate 68 %, "no instruction" 4.7 stall cycles per issue at 12
+// warps); a called register-to-register product passes its operands through the stack.  uprod
+// loads its multiplicands into registers, streams the other operands one limb per row from the
+// slots and writes the result back, so nothing is live across a call, the kernel needs the
+// registers of one product, and all warps of an SM loop in the same 18 KB of code.
+template <class F>
+struct SmemXYZZ {
+    static constexpr int N = F::N;
+    uint32_t *base;  // this thread's column of the block's slots
+    int stride;      // words between consecutive limbs = threads per block
+    bool inf;        // the accumulator is the neutral element (its slots are then meaningless)
+    enum { SX = 0, SY = 1, SZZ = 2, SZZZ = 3, ST0 = 4, ST1 = 5, ST2 = 6, ST3 = 7, NONE = -1 };
+
+    B200_DEV SmemXYZZ(uint32_t *smem, int tid, int threads) : base(smem + tid), stride(threads), inf(true) {}
+    B200_DEV static uint32_t *slot_of(uint32_t *base, int stride, int e) { return base + (size_t)e * N * stride; }
+    B200_DEV uint32_t *slot(int e) const { return slot_of(base, stride, e); }
+
+    // dst <- a b [- c d] [- s]   (slot numbers; c = NONE: one product; s = NONE: no subtraction).
+    // The two-product form shares one Montgomery reduction (Fp::mul2).
+    __device__ __noinline__ static void uprod(uint32_t *base, int stride, int dst, int a, int b, int c,
+                                              int d, int s) {
+        const uint32_t *sb = slot_of(base, stride, b);
+        const bool two = c != NONE;
+        const uint32_t *sd = slot_of(base, stride, two ? d : b);
+        const F A = F::lds(slot_of(base, stride, a), stride);
+        F Cn = F::zero();
+        if (two) Cn = F::neg(F::lds(slot_of(base, stride, c), stride));
+        uint32_t E[N], O[N];
+        uint32_t b0 = sb[0], b1 = sb[stride], d0 = sd[0], d1 = sd[stride];
+        if (two) {
+            F::mont_row2(E, O, A.v, b0, Cn.v, d0, true);
+            F::mont_row2(O, E, A.v, b1, Cn.v, d1, false);
+        } else {
+            F::mont_row(E, O, A.v, b0, true);
+            F::mont_row(O, E, A.v, b1, false);
+        }
+#pragma unroll 1
+        for (int it = 1; it < N / 2; it++) {
+            const size_t o = (size_t)(2 * it) * stride;
+            b0 = sb[o], b1 = sb[o + stride];
+            if (two) {
+                d0 = sd[o], d1 = sd[o + stride];
+                F::mont_row2(E, O, A.v, b0, Cn.v, d0, false);
+                F::mont_row2(O, E, A.v, b1, Cn.v, d1, false);
+            } else {
+                F::mont_row(E, O, A.v, b0, false);
+                F::mont_row(O, E, A.v, b1, false);
+            }
+        }
+        F r = F::finish(E, O);
+        if (s != NONE) r = F::sub(r, F::lds(slot_of(base, stride, s), stride));
+        r.sts(slot_of(base, stride, dst), stride);
+    }
+    B200_DEV void prod(int dst, int a, int b, int s = NONE) const { uprod(base, stride, dst, a, b, NONE, NONE, s); }
+    // Two independent products at once: d1 <- a1 b1 [- s1], d2 <- a2 b2 [- s2].  With two warps per
+    // scheduler a single product's carry chains leave the multiply pipe waiting on their own
+    // latency (ncu: 3.3 "wait" stall cycles per issue); the rows of two products interleave into
+    // twice the independent chains.
+    __device__ __noinline__ static void uprod_pair(uint32_t *base, int stride, int d1, int a1, int b1,
+                                                   int s1, int d2, int a2, int b2, int s2) {
+        const uint32_t *p1 = slot_of(base, stride, b1), *p2 = slot_of(base, stride, b2);
+        const F A1 = F::lds(slot_of(base, stride, a1), stride), A2 = F::lds(slot_of(base, stride, a2), stride);
+        uint32_t E1[N], O1[N], E2[N], O2[N];
+        F::mont_row(E1, O1, A1.v, p1[0], true);
+        F::mont_row(E2, O2, A2.v, p2[0], true);
+        F::mont_row(O1, E1, A1.v, p1[stride], false);
+        F::mont_row(O2, E2, A2.v, p2[stride], false);
+#pragma unroll 1
+        for (int it = 1; it < N / 2; it++) {
+            const size_t o = (size_t)(2 * it) * stride;
+            const uint32_t x0 = p1[o], x1 = p1[o + stride], y0 = p2[o], y1 = p2[o + stride];
+            F::mont_row(E1, O1, A1.v, x0, false);
+            F::mont_row(E2, O2, A2.v, y0, false);
+            F::mont_row(O1, E1, A1.v, x1, false);
+            F::mont_row(O2, E2, A2.v, y1, false);
+        }
+        F r = F::finish(E1, O1);
+        if (s1 != NONE) r = F::sub(r, F::lds(slot_of(base, stride, s1), stride));
+        r.sts(slot_of(base, stride, d1), stride);
+        r = F::finish(E2, O2);
+        if (s2 != NONE) r = F::sub(r, F::lds(slot_of(base, stride, s2), stride));
+        r.sts(slot_of(base, stride, d2), stride);
+    }
+    B200_DEV void pair(int d1, int a1, int b1, int s1, int d2, int a2, int b2, int s2) const {
+        uprod_pair(base, stride, d1, a1, b1, s1, d2, a2, b2, s2);
+    }
+    B200_DEV bool is_zero(int a) const {
+        const uint32_t *p = slot(a);
+        uint32_t o = 0;
+#pragma unroll
+        for (int i = 0; i < N; i++) o |= p[(size_t)i * stride];
+        return o == 0;
+    }
+
+    // (out of line like the products: the entry function stays the segment walk alone)
+    __device__ __noinline__ static void store_slots(uint32_t *base, int stride, uint32_t *dst, bool inf) {
+        if (inf) {
+            XYZZ<F>::inf().store(dst);
+            return;
+        }
+#pragma unroll 1
+        for (int e = 0; e < 4; e++) F::lds(slot_of(base, stride, e), stride).store(dst + e * N);
+    }
+    B200_DEV void store_global(uint32_t *dst) const { store_slots(base, stride, dst, inf); }
+    // slots (ex, ey) <- (x2, +-y2): vector loads from global memory (with most of the SM's L1
+    // carved out as shared memory, limb-wise reads of global memory would all go to the L2)
+    __device__ __noinline__ static void stage_point(uint32_t *base, int stride, const uint32_t *gp,
+                                                    bool negate, int ex, int ey) {
+        F::load(gp).sts(slot_of(base, stride, ex), stride);
+        F::cneg(F::load(gp + N), negate).sts(slot_of(base, stride, ey), stride);
+    }
+    B200_DEV void set_one(int e) const { F::one().sts(slot(e), stride); }
+
+    // acc += (x2, +-y2), the affine point at gp (not infinity); madd-2008-s as XYZZ::madd
+    B200_DEV void madd(const uint32_t *gp, bool negate) {
+        if (inf) {
+            stage_point(base, stride, gp, negate, SX, SY);
+            set_one(SZZ), set_one(SZZZ);
+            inf = false;
+            return;
+        }
+        stage_point(base, stride, gp, negate, ST0, ST1);
+        pair(ST0, SZZ, ST0, SX, ST1, SZZZ, ST1, SY);          // Pd = x2 ZZ - X, R = +-y2 ZZZ - Y
+        if (is_zero(ST0)) {                                   // same x: P + P or P - P
+            if (is_zero(ST1))
+                set_double(gp, negate);
+            else
+                inf = true;
+            return;
+        }
+        pair(ST2, ST0, ST0, NONE, ST3, ST1, ST1, NONE);       // PP = Pd^2, R^2
+        pair(ST0, ST2, ST0, NONE, SZZ, SZZ, ST2, NONE);       // PPP = PP Pd, ZZ PP
+        pair(SX, SX, ST2, NONE, SZZZ, SZZZ, ST0, NONE);       // Q = X PP, ZZZ PPP
+        {
+            const F Q = F::lds(slot(SX), stride);
+            const F X3 = F::sub(F::sub(F::lds(slot(ST3), stride), F::lds(slot(ST0), stride)), F::dbl(Q));
+            X3.sts(slot(SX), stride);                         // R^2 - PPP - 2 Q
+            F::sub(Q, X3).sts(slot(ST2), stride);             // Q - X3
+        }
+        uprod(base, stride, SY, ST2, ST1, SY, ST0, NONE);     // Y3 = (Q - X3) R - Y PPP
+    }
+    // slots <- 2 (x2, +-y2): mdbl-2008-s-1 as XYZZ::dbl_affine, as a slot program
+    B200_DEV void set_double(const uint32_t *gp, bool negate) {
+        stage_point(base, stride, gp, negate, SX, SY);
+        {
+            const F y = F::lds(slot(SY), stride);
+            F::dbl(y).sts(slot(ST0), stride);            // U = 2 y
+        }
+        pair(SZZ, ST0, ST0, NONE, ST2, SX, SX, NONE);      // V = U^2 = ZZ, x^2
+        pair(SZZZ, ST0, SZZ, NONE, ST1, SX, SZZ, NONE);    // W = U V = ZZZ, S = x V
+        {
+            const F t = F::lds(slot(ST2), stride);
+            t.sts(slot(ST0), stride);
+        }
+        {
+            const F xx = F::lds(slot(ST0), stride);
+            F::add(F::dbl(xx), xx).sts(slot(ST0), stride);   // M = 3 x^2
+        }
+        prod(SX, ST0, ST0);                 // M^2
+        {
+            const F S = F::lds(slot(ST1), stride);
+            const F X3 = F::sub(F::lds(slot(SX), stride), F::dbl(S));
+            X3.sts(slot(SX), stride);
+            F::sub(S, X3).sts(slot(ST1), stride);        // S - X3
+        }
+        uprod(base, stride, SY, ST1, ST0, SZZZ, SY, NONE);  // Y3 = (S - X3) M - W y
+    }
+};
+
+template <class C>
+__global__ void __launch_bounds__(SmemAccum<C>::THREADS, B200_SM_MINBLOCKS)
+    k_accum_first_sm(const Entry *__restrict__ sorted, const uint32_t *__restrict__ offsets,
+                     const uint32_t *__restrict__ seg_bucket, uint32_t total, uint32_t SEG,
+                     uint32_t t_begin, uint32_t t_end, const uint32_t *__restrict__ aff,
+                     uint32_t *__restrict__ bucket_acc, uint32_t *__restrict__ carry_key,
+                     uint32_t *__restrict__ carry_pt, uint32_t key_base) {
+    using R = Raw<C>;
+    using F = AccumField<typename C::Fq>;
+    using X = XYZZ<F>;
+    extern __shared__ uint32_t smem_acc[];
+    const uint32_t t = t_begin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= t_end) return;
+    const uint64_t start64 = (uint64_t)t * SEG;
+    if (start64 >= total) return;
+    const uint32_t start = (uint32_t)start64;
+    const uint32_t end = (uint32_t)min((uint64_t)total, start64 + SEG);
+
+    uint32_t cur = seg_bucket[t];
+    uint32_t next = offsets[cur + 1];            // first position of the following bucket
+    bool head_carry = start > offsets[cur];      // the bucket began in an earlier segment
+    carry_key[t] = key_base + cur;
+    bool carried = false;
+    SmemXYZZ<F> acc(smem_acc, (int)threadIdx.x, (int)blockDim.x);
+    uint4 q = *reinterpret_cast<const uint4 *>(sorted + start);  // 4 items per load
+    Entry e = q.x;
+    for (uint32_t pos = start; pos < end; pos++) {
+        const Entry ecur = e;
+        if (pos + 1 < end) {  // the next item; its point only as an L2 prefetch
+            const uint32_t k = (pos + 1 - start) & 3u;
+            if (k == 0) q = *reinterpret_cast<const uint4 *>(sorted + pos + 1);
+            e = k == 0 ? q.x : k == 1 ? q.y : k == 2 ? q.z : q.w;
+            const char *np = reinterpret_cast<const char *>(aff + (size_t)(e & 0x7fffffffu) * R::AW);
+#pragma unroll
+            for (int o = 0; o < R::AW * 4; o += 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(np + o));
+        }
+        if (pos == next) {  // the run of `cur` is complete; `pos` starts a later, non-empty bucket
+            if (head_carry && !carried) {
+                acc.store_global(carry_pt + (size_t)t * R::XW);
+                carried = true;
+            } else {
+                acc.store_global(bucket_acc + (size_t)cur * R::XW);
+            }
+            head_carry = false;
+            do {
+                cur++;
+                next = offsets[cur + 1];
+            } while (next <= pos);  // skip empty buckets
+            acc.inf = true;
+        }
+        acc.madd(aff + (size_t)(ecur & 0x7fffffffu) * R::AW, (ecur >> 31) != 0);
+    }
+    if (head_carry && !carried) {
+        acc.store_global(carry_pt + (size_t)t * R::XW);
+        carried = true;
+    } else {
+        acc.store_global(bucket_acc + (size_t)cur * R::XW);
+    }
+    if (!carried) X::inf().store(carry_pt + (size_t)t * R::XW);
+}
+
 // Later rounds: the carry list (keys ascending, one XYZZ point each) is reduced the same way with
 // full additions; sums of runs that begin a bucket in this list are added into bucket_acc.
 // The list is entries [begin, end) of keys / pts; only keys in [key_lo, key_hi) are live (a group
