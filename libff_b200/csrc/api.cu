@@ -274,13 +274,21 @@ void pick_bounds(const Ctx &ctx, size_t n, size_t parts, size_t *bounds, bool sc
     const double g = ctx.opt_h2d_growth > 0 ? ctx.opt_h2d_growth / 100.0
                      : scalars_only ? 2.0
                      : (ctx.opt_h2d_shared_buckets && parts > 5) ? 1.2 : 1.3;
-    double total = 0, w = 1;
-    for (size_t k = 0; k < parts; k++, w *= g) total += w;
+    // weights: geometric growth from the first range; with h2d_taper the trailing ranges shrink
+    // again (the last range's computation overlaps no upload either)
+    auto weight = [&](size_t k) {
+        size_t e = k;
+        if (ctx.opt_h2d_taper) e = std::min(k, (parts - 1 - k) * (size_t)ctx.opt_h2d_taper);
+        double w = 1;
+        for (size_t q = 0; q < e; q++) w *= g;
+        return w;
+    };
+    double total = 0;
+    for (size_t k = 0; k < parts; k++) total += weight(k);
     double acc = 0;
-    w = 1;
     bounds[0] = 0;
-    for (size_t k = 0; k + 1 < parts; k++, w *= g) {
-        acc += w;
+    for (size_t k = 0; k + 1 < parts; k++) {
+        acc += weight(k);
         size_t b = (size_t)((double)n * (acc / total));
         if (n >= ((size_t)1 << 16)) b &= ~(size_t)255;  // 16-byte aligned ranges in all arrays
         bounds[k + 1] = std::min(std::max(b, bounds[k]), n);
@@ -1644,6 +1652,7 @@ bool b200msm_set_option(const char *name, int64_t value) {
         {"h2d_parts", &Ctx::opt_h2d_parts, 0, MAX_H2D_PARTS},
         {"h2d_pack", &Ctx::opt_h2d_pack, 0, 2},
         {"stage_lanes", &Ctx::opt_stage_lanes, 1, STAGE_LANES_MAX},
+        {"h2d_taper", &Ctx::opt_h2d_taper, 0, 8},
         {"sort_overlap", &Ctx::opt_sort_overlap, 0, 64},
         {"coop_accum", &Ctx::opt_coop_accum, 0, 2},
     };

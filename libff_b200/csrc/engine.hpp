@@ -153,7 +153,10 @@ struct Ctx {
     int opt_window_groups = 0; // groups the windows are walked in (top-down); 0 = automatic, 1 = one
     int opt_carry_segment = 0; // carries per thread in the later accumulation rounds; 0 = automatic
     int opt_reduce_chunk = 0; // log2 of the buckets per thread in the reduction; 0 = automatic
-    int opt_h2d_pack = 1;     // special-form bases leave Z behind on upload: 0 never, 1 pageable sources, 2 always
+    // special-form bases leave Z behind on upload: 0 never (default: measured, the host-side packing
+    // loses to the plain copy on a 16-core host, profiles/pack_sweep_r02.log), 1 pageable sources, 2 always
+    int opt_h2d_pack = 0;
+    int opt_h2d_taper = 0;    // trailing upload ranges shrink again (steps of growth per range from the end); 0 = off
     int opt_stage_lanes = 8;  // host threads that stage pageable buffers through the pinned ring
     int opt_sort_overlap = 0; // window groups whose sort overlaps the previous accumulation; 0 = automatic
     int opt_coop_accum = 0;   // lane-cooperative accumulation of the wide fields: 0 automatic, 1 off, 2 on

@@ -31,8 +31,10 @@ hb = torch.from_numpy(bases).pin_memory()
 hs = torch.from_numpy(scalars).pin_memory()
 growths = [int(x) for x in os.environ.get("GROWTH", "0").split(",")]
 shareds = [int(x) for x in os.environ.get("SHARED", "1").split(",")]
-for sh, p, gr in [(sh, p, gr) for sh in shareds for p in parts for gr in growths]:
+tapers = [int(x) for x in os.environ.get("TAPER", "0").split(",")]
+for sh, p, gr, tp in [(sh, p, gr, tp) for sh in shareds for p in parts for gr in growths for tp in tapers]:
     m.set_option("h2d_shared_buckets", sh)
+    m.set_option("h2d_taper", tp)
     m.set_option("h2d_parts", p)
     m.set_option("h2d_growth", gr)
     best = 1e9
@@ -41,4 +43,4 @@ for sh, p, gr in [(sh, p, gr) for sh in shareds for p in parts for gr in growths
         got = m.multi_exp_host_ptr(gid, hb.data_ptr(), hs.data_ptr(), n)
         best = min(best, m.timer_stop())
     ok = bool(np.array_equal(m.batch_to_special(gid, got.reshape(1, -1))[0], want))
-    print(f"shared={sh} h2d_parts={p} growth={gr}: e2e {best:.2f} ms = {n / best / 1e3:.1f} M points/s  same={ok}", flush=True)
+    print(f"shared={sh} h2d_parts={p} growth={gr} taper={tp}: e2e {best:.2f} ms = {n / best / 1e3:.1f} M points/s  same={ok}", flush=True)
