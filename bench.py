@@ -79,23 +79,23 @@ def ncu_capture(group, log2n):
                                          "dram__bytes_write.sum",
                                          "sm__pipe_fmaheavy_cycles_active.avg.pct_of_peak_sustained_elapsed")}
         units = rows[1]
-        best = None
-        for r in rows[2:]:
-            if "k_accum" not in r[col["Kernel Name"]]:
-                continue
-            if best is None or float(r[col["gpu__time_duration.sum"]]) > float(best[col["gpu__time_duration.sum"]]):
-                best = r
-        if best is None:
+        # the capture holds the kernel's launches of ONE step (one per window group): totals over
+        # them, the pipe utilisation weighted by launch time
+        picked = [r for r in rows[2:] if "k_accum" in r[col["Kernel Name"]]]
+        if not picked:
             return None
         scale = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}
 
-        def nbytes(k):
-            return float(best[col[k]]) * scale.get(units[col[k]], 1.0)
+        def nbytes(r, k):
+            return float(r[col[k]]) * scale.get(units[col[k]], 1.0)
 
-        return {"file": os.path.relpath(path, ROOT),
-                "kernel_ms_under_ncu": float(best[col["gpu__time_duration.sum"]]),
-                "traffic": nbytes("dram__bytes_read.sum") + nbytes("dram__bytes_write.sum"),
-                "fmaheavy": float(best[col["sm__pipe_fmaheavy_cycles_active.avg.pct_of_peak_sustained_elapsed"]]) / 100}
+        ms = [float(r[col["gpu__time_duration.sum"]]) for r in picked]
+        fm = [float(r[col["sm__pipe_fmaheavy_cycles_active.avg.pct_of_peak_sustained_elapsed"]]) for r in picked]
+        return {"file": os.path.relpath(path, ROOT), "launches": len(picked),
+                "kernel_ms_under_ncu": sum(ms),
+                "traffic": sum(nbytes(r, "dram__bytes_read.sum") + nbytes(r, "dram__bytes_write.sum")
+                               for r in picked),
+                "fmaheavy": sum(a * b for a, b in zip(ms, fm)) / sum(ms) / 100}
     except Exception as e:  # a capture in another layout: say so instead of guessing
         return {"file": os.path.relpath(path, ROOT), "error": str(e)}
 
@@ -553,8 +553,8 @@ def main():
         "traffic": cap.get("traffic") if cap else None,
         "pipe_utilisation_ncu": cap.get("fmaheavy") if cap else None,
         "ncu_capture": cap,
-        "traffic_unit": "bytes per launch (ncu dram read + write); algorithmic gather = items x "
-                        "(affine point + 4-byte item)",
+        "traffic_unit": "bytes per step = all launches of the kernel in one MSM (ncu dram read + "
+                        "write); algorithmic gather = items x (affine point + 4-byte item)",
         "hbm_stream": {"achieved_GBps": n * MIN_BYTES[gid] / (phase_ms["total"] * 1e-3) / 1e9,
                        "peak_GBps": hbm_peak, "note": "secondary counter; the path is not HBM-bound"},
     }

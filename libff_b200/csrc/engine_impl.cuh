@@ -213,8 +213,14 @@ MsmGeom<C> msm_geom(const Ctx &ctx, size_t n, const MsmShape *shape) {
     return g;
 }
 
+// Measured (profiles/sweep_sort_r02.log): the overlap hides the sort -- at 2^24 the exposed digit
+// pass falls from 2.0 to 0.5 ms and the scatter from 2.35 to 0.2 ms -- but the accumulation grows
+// by the same 3.6 ms (42.04 against 42.14 ms in total; within 1 % at 2^20..2^22 too): its blocks
+// hold every register of an SM, so the sort's blocks only run in slots an accumulation block gave
+// up.  The groups therefore stay an option (sort_overlap > 1); the default is one sort, which also
+// keeps the phase timings of a call disjoint.
 #ifndef B200_SORT_OVERLAP_MIN_LOG2
-#define B200_SORT_OVERLAP_MIN_LOG2 24
+#define B200_SORT_OVERLAP_MIN_LOG2 62
 #endif
 // Groups of windows (ascending).  The counting sort of group g + 1 -- digit pass, scan, scatter:
 // L2-atomic / random-access bound -- runs on the sort stream under the accumulation of group g,
