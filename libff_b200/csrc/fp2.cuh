@@ -45,7 +45,9 @@ struct Fp2 {
         }
     }
     // (a0 + a1 u)(b0 + b1 u) = (a0 b0 - NR a1 b1) + ((a0 + a1)(b0 + b1) - a0 b0 - a1 b1) u
-    __device__ __noinline__ static Fp2 mul(const Fp2 &a, const Fp2 &b) {
+    // (out of line, operands BY VALUE: they travel in registers; by reference they would sit in
+    // local memory -- 224 local loads / stores around every call in a product chain)
+    __device__ __noinline__ static Fp2 mul(Fp2 a, Fp2 b) {
         F v0 = F::mul(a.c0, b.c0);
         F v1 = F::mul(a.c1, b.c1);
         F s = F::mul(F::add(a.c0, a.c1), F::add(b.c0, b.c1));
@@ -63,7 +65,7 @@ struct Fp2 {
         return add(mul(a, b), mul(c, d));
     }
     // (a0 + a1 u)^2 = (a0 + a1)(a0 - NR a1) + (NR - 1) a0 a1 + 2 a0 a1 u   (fp2.tcc:141-151)
-    __device__ __noinline__ static Fp2 sqr(const Fp2 &a) {
+    __device__ __noinline__ static Fp2 sqr(Fp2 a) {
         F t = F::mul(a.c0, a.c1);
         F c0 = F::mul(F::add(a.c0, a.c1), F::sub(a.c0, times_nr(a.c1)));
         if constexpr (NR == 5) c0 = F::add(c0, F::dbl(F::dbl(t)));

@@ -707,13 +707,34 @@ __global__ void __launch_bounds__(64)
     if (j >= chunks) return;
     const uint32_t lo = j * K, hi = lo + K;
     X running = X::inf(), acc = X::inf();
-    for (uint32_t b = hi; b-- > lo;) {
-        const size_t g = (size_t)w * B + b;
-        if (hist[g] != 0) {  // empty buckets were never written
-            X q = X::load(bucket_acc + g * R::XW);
-            X::add(running, q);
+    if constexpr (!BaseLimbs<typename C::Fq>::EXT && BaseLimbs<typename C::Fq>::N <= 8) {
+        // Short prime fields: ONE inlined addition site serves both steps of a bucket (running +=
+        // bucket, acc += running), its operands picked by selects.  The out-of-line addition takes
+        // its points from local memory; here they stay in registers.
+        for (uint32_t b = hi; b-- > lo;) {
+            const size_t g = (size_t)w * B + b;
+            X q = X::inf();
+            if (hist[g] != 0) q = X::load(bucket_acc + g * R::XW);  // empty buckets were never written
+#pragma unroll 1
+            for (int step = 0; step < 2; step++) {
+                X dst = X::select(step == 0, running, acc);
+                const X src = X::select(step == 0, q, running);
+                X::add_inline(dst, src);
+                if (step == 0)
+                    running = dst;
+                else
+                    acc = dst;
+            }
         }
-        X::add(acc, running);
+    } else {
+        for (uint32_t b = hi; b-- > lo;) {
+            const size_t g = (size_t)w * B + b;
+            if (hist[g] != 0) {  // empty buckets were never written
+                X q = X::load(bucket_acc + g * R::XW);
+                X::add(running, q);
+            }
+            X::add(acc, running);
+        }
     }
     acc.store(chunk_L + ((size_t)w * chunks + j) * R::XW);
     running.store(chunk_T + ((size_t)w * chunks + j) * R::XW);
@@ -739,13 +760,34 @@ __global__ void __launch_bounds__(THREADS)
     X total = X::inf(), plain = X::inf();
     if (t * Q < chunks) {
         X sumL = X::inf(), run = X::inf(), acc = X::inf();
-        for (uint32_t j = (t + 1) * Q; j-- > t * Q;) {
-            const size_t g = ((size_t)w * chunks + j) * R::XW;
-            X::add(acc, run);  // T_j is counted (j - tQ) times: once per later step
-            X q = X::load(chunk_T + g);
-            X::add(run, q);
-            q = X::load(chunk_L + g);
-            X::add(sumL, q);
+        if constexpr (!BaseLimbs<typename C::Fq>::EXT && BaseLimbs<typename C::Fq>::N <= 8) {
+            // one inlined addition site for the three steps of a chunk (see k_bucket_reduce)
+            for (uint32_t j = (t + 1) * Q; j-- > t * Q;) {
+                const size_t g = ((size_t)w * chunks + j) * R::XW;
+                const X qT = X::load(chunk_T + g), qL = X::load(chunk_L + g);
+#pragma unroll 1
+                for (int step = 0; step < 3; step++) {
+                    // acc += run;  run += T_j;  sumL += L_j
+                    X dst = step == 0 ? acc : step == 1 ? run : sumL;
+                    const X src = step == 0 ? run : step == 1 ? qT : qL;
+                    X::add_inline(dst, src);
+                    if (step == 0)
+                        acc = dst;
+                    else if (step == 1)
+                        run = dst;
+                    else
+                        sumL = dst;
+                }
+            }
+        } else {
+            for (uint32_t j = (t + 1) * Q; j-- > t * Q;) {
+                const size_t g = ((size_t)w * chunks + j) * R::XW;
+                X::add(acc, run);  // T_j is counted (j - tQ) times: once per later step
+                X q = X::load(chunk_T + g);
+                X::add(run, q);
+                q = X::load(chunk_L + g);
+                X::add(sumL, q);
+            }
         }
         plain = run;
         X y = small_mul<F>(run, t);

@@ -55,7 +55,7 @@ struct XYZZ {
     B200_DEV static XYZZ neg(const XYZZ &p) { return XYZZ{p.X, F::neg(p.Y), p.ZZ, p.ZZZ}; }
 
     // 2 * (x, y), affine input, not infinity
-    __device__ __noinline__ static XYZZ dbl_affine(const F &x, const F &y) {
+    __device__ __noinline__ static XYZZ dbl_affine(F x, F y) {
         F U = F::dbl(y);
         F V = F::sqr(U);
         F W = F::mul(U, V);
@@ -67,7 +67,7 @@ struct XYZZ {
         return XYZZ{X3, Y3, V, W};
     }
 
-    __device__ __noinline__ static XYZZ dbl(const XYZZ &p) {
+    __device__ __noinline__ static XYZZ dbl(XYZZ p) {
         if (p.is_inf()) return p;
         F U = F::dbl(p.Y);
         F V = F::sqr(U);
@@ -107,7 +107,17 @@ struct XYZZ {
     }
 
     // acc += q
-    __device__ __noinline__ static void add(XYZZ &acc, const XYZZ &q) {
+    // (out of line with the points BY VALUE: what fits travels in registers instead of through
+    // local memory)
+    __device__ __noinline__ static XYZZ add_value(XYZZ acc, XYZZ q) {
+        add_inline(acc, q);
+        return acc;
+    }
+    B200_DEV static void add(XYZZ &acc, const XYZZ &q) { acc = add_value(acc, q); }
+    // the same inlined at the call site: no operands through the stack (the out-of-line routine
+    // takes its points by reference, i.e. from local memory); for kernels that have ONE addition
+    // site and a field short enough for the code to stay cached
+    B200_DEV static void add_inline(XYZZ &acc, const XYZZ &q) {
         if (q.is_inf()) return;
         if (acc.is_inf()) {
             acc = q;
@@ -133,6 +143,10 @@ struct XYZZ {
         acc.Y = Y3;
         acc.ZZ = F::mul(F::mul(acc.ZZ, q.ZZ), PP);
         acc.ZZZ = F::mul(F::mul(acc.ZZZ, q.ZZZ), PPP);
+    }
+    B200_DEV static XYZZ select(bool flag, const XYZZ &a, const XYZZ &b) {  // flag ? a : b
+        return XYZZ{F::select(flag, a.X, b.X), F::select(flag, a.Y, b.Y), F::select(flag, a.ZZ, b.ZZ),
+                    F::select(flag, a.ZZZ, b.ZZZ)};
     }
 
     // Representatives in the reference's coordinate systems (no inversion needed):
