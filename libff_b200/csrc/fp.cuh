@@ -353,7 +353,7 @@ struct Fp {
         }
         return finish(E, O);
     }
-    __device__ __noinline__ static Fp mul_call(const Fp &a, const Fp &b) { return mul_inline(a, b); }
+    __device__ __noinline__ static Fp mul_call(Fp a, Fp b) { return mul_inline(a, b); }  // by value: registers
     B200_DEV static Fp mul_inline(const Fp &a, const Fp &b) {
         uint32_t E[N], O[N];
 #pragma unroll
@@ -375,7 +375,7 @@ struct Fp {
         else
             return sqr_inline(a);
     }
-    __device__ __noinline__ static Fp sqr_call(const Fp &a) { return sqr_inline(a); }
+    __device__ __noinline__ static Fp sqr_call(Fp a) { return sqr_inline(a); }
     B200_DEV static Fp sqr_inline(const Fp &a) {
         uint32_t a2[N];  // 2a fits: the top limb has spare bits
         asm volatile("add.cc.u32 %0, %1, %1;" : "=r"(a2[0]) : "r"(a.v[0]));
@@ -414,7 +414,7 @@ struct Fp {
         }
         return finish(E, O);
     }
-    __device__ __noinline__ static Fp mul2_call(const Fp &a, const Fp &b, const Fp &c, const Fp &d) {
+    __device__ __noinline__ static Fp mul2_call(Fp a, Fp b, Fp c, Fp d) {
         return mul2_inline(a, b, c, d);
     }
     B200_DEV static Fp mul2_inline(const Fp &a, const Fp &b, const Fp &c, const Fp &d) {
@@ -505,7 +505,7 @@ struct Fp {
 
     // a^(p-2): the canonical inverse, equal to the reference's invert() output (the inverse in
     // [0, p) is unique).  inv(0) = 0.
-    __device__ __noinline__ static Fp inv(const Fp &a) {
+    __device__ __noinline__ static Fp inv(Fp a) {
         Fp r = one();
 #pragma unroll 1
         for (int i = P::BITS - 1; i >= 0; i--) {

@@ -54,7 +54,7 @@ struct Fp2 {
         return Fp2{F::sub(v0, times_nr(v1)), F::sub(F::sub(s, v0), v1)};
     }
     // the same with the three base-field products on the FP64 pipe (fp_dfma.cuh)
-    __device__ __noinline__ static Fp2 mul_d(const Fp2 &a, const Fp2 &b) {
+    __device__ __noinline__ static Fp2 mul_d(Fp2 a, Fp2 b) {
         F v0 = F::mul_d(a.c0, b.c0);
         F v1 = F::mul_d(a.c1, b.c1);
         F s = F::mul_d(F::add(a.c0, a.c1), F::add(b.c0, b.c1));
@@ -72,7 +72,7 @@ struct Fp2 {
         return Fp2{c0, F::dbl(t)};
     }
     // 1 / (a0 + a1 u) = (a0 - a1 u) / (a0^2 + NR a1^2)
-    __device__ __noinline__ static Fp2 inv(const Fp2 &a) {
+    __device__ __noinline__ static Fp2 inv(Fp2 a) {
         F d = F::inv(F::add(F::sqr(a.c0), times_nr(F::sqr(a.c1))));
         return Fp2{F::mul(a.c0, d), F::neg(F::mul(a.c1, d))};
     }

@@ -176,7 +176,7 @@ struct XYZZ {
 
 // k * p for a small non-negative k (double-and-add, MSB first)
 template <class F>
-__device__ __noinline__ XYZZ<F> small_mul(const XYZZ<F> &p, uint32_t k) {
+__device__ __noinline__ XYZZ<F> small_mul(XYZZ<F> p, uint32_t k) {
     XYZZ<F> r = XYZZ<F>::inf();
     if (k == 0 || p.is_inf()) return r;
     for (int bit = 31 - __clz(k); bit >= 0; bit--) {
