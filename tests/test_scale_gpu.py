@@ -13,7 +13,7 @@ with DEFAULT options on
 
 against the unmodified reference's multi_exp<BDLO12, special>(chunks = host threads) on the same
 SHA512_rng scalars and arithmetic-walk bases, limb for limb after normalisation -- resident inputs,
-pageable host buffers (packed upload) and the ranged upload pipeline -- and at 2^22 / 2^24 / 2^26
+pageable host buffers (plain and packed upload) and the ranged upload pipeline -- and at 2^22 / 2^24 / 2^26
 against the closed form (sum_i s_i (a + i d)) G, computed with numpy / Python integers and ONE
 reference scalar multiplication, independent of any MSM code.
 """
@@ -78,7 +78,7 @@ def test_config_size_matches_reference_multi_exp(engine, ref, workloads, gid, lo
     part = ref.multi_exp(gid, bases[lo:lo + cnt], scalars[lo:lo + cnt], chunks=threads())
     np.testing.assert_array_equal(affine(engine, gid, engine.multi_exp_resident(rb, rs, lo, cnt)),
                                   part, err_msg="resident sub-range")
-    # 2. host buffers, default options (pageable numpy memory: staged, special form packed)
+    # 2. host buffers, default options (pageable numpy memory: staged, full elements travel)
     np.testing.assert_array_equal(affine(engine, gid, engine.multi_exp(gid, bases, scalars)), want,
                                   err_msg="host buffers")
     # 3. the ranged upload pipeline (what n >= 2^23 takes by default): 12 ranges, one bucket set
@@ -86,10 +86,10 @@ def test_config_size_matches_reference_multi_exp(engine, ref, workloads, gid, lo
     try:
         np.testing.assert_array_equal(affine(engine, gid, engine.multi_exp(gid, bases, scalars)),
                                       want, err_msg="12 upload ranges, shared buckets")
-        engine.set_option("h2d_pack", 0)  # full elements travel, Z dropped on the device
+        engine.set_option("h2d_pack", 1)  # special-form bases packed to X|Y on the host
         np.testing.assert_array_equal(affine(engine, gid, engine.multi_exp(gid, bases, scalars)),
-                                      want, err_msg="12 upload ranges, unpacked")
-        engine.set_option("h2d_pack", 1)
+                                      want, err_msg="12 upload ranges, packed")
+        engine.set_option("h2d_pack", 0)
         # 4. the prover's shape: resident bases, host scalars in ranges
         np.testing.assert_array_equal(affine(engine, gid, engine.multi_exp_resident_bases(rb, scalars)),
                                       want, err_msg="resident bases, host scalars")
@@ -98,7 +98,7 @@ def test_config_size_matches_reference_multi_exp(engine, ref, workloads, gid, lo
                                       want, err_msg="12 independent ranges")
     finally:
         engine.set_option("h2d_parts", 0)
-        engine.set_option("h2d_pack", 1)
+        engine.set_option("h2d_pack", 0)
         engine.set_option("h2d_shared_buckets", 1)
     # 5. one sort for all windows against the overlapped window groups
     engine.set_option("sort_overlap", 1)
