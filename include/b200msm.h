@@ -130,6 +130,22 @@ bool b200msm_sum(uint32_t group, const void *points, size_t points_bytes, size_t
  * Output is canonical (Z = 1; zero -> (0, 1, 0)) and equals the reference's limb for limb. */
 bool b200msm_batch_to_special(uint32_t group, void *inout, size_t bytes, size_t n);
 
+/* No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  batch_to_special on DEVICE memory that allocates nothing: `d_in` and `d_out` are
+ * device pointers to n group elements in reference layout on the CURRENT device (they may be the
+ * same buffer), bytes == n * sizeof(GroupT); the kernels are enqueued on `cuda_stream` (a
+ * cudaStream_t, NULL = the default stream) and the call returns without synchronising.  The result
+ * equals b200msm_batch_to_special's limb for limb.  The inversion tree's scratch is a file-scope
+ * `static __device__` array of 6.4 MiB that every GPU loading the library holds until exit, so
+ * n <= B200MSM_NOALLOC_MAX_POINTS per call (larger n is refused with an error; split the batch).
+ * The call performs no cudaMalloc / cudaFree and needs no b200msm_init.  All calls on a device
+ * share the array (it keeps the previous call's contents; nothing in it needs clearing): calls
+ * that overlap on the GPU -- different streams or host threads -- race and must be serialised. */
+#define B200MSM_NOALLOC_MAX_POINTS 32768u
+bool b200msm_batch_to_special_noalloc(uint32_t group, const void *d_in, void *d_out, size_t bytes,
+                                      size_t n, void *cuda_stream);
+
 /* libff::batch_exp<G, Fr>(scalar_size, window, table, v) (multiexp.tcc:875-915).  window_table<G>
  * is vector<vector<G>> (multiexp.hpp:101): pass one pointer per row, each row `row_len`
  * (= 1 << window) elements (multiexp.tcc:809-846).  num_rows must equal

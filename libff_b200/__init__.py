@@ -59,7 +59,7 @@ ABI_SYMBOLS = [
     "b200msm_init_devices", "b200msm_init_all", "b200msm_device_count",
     "b200msm_multi_exp_resident_bases", "b200msm_batch_exp_with_coeff", "b200msm_table_upload",
     "b200msm_table_build", "b200msm_table_shape", "b200msm_table_download",
-    "b200msm_batch_exp_resident", "b200msm_device_timings",
+    "b200msm_batch_exp_resident", "b200msm_device_timings", "b200msm_batch_to_special_noalloc",
 ]
 
 
@@ -102,6 +102,7 @@ def load():
         "b200msm_release": (C.c_bool, [u64]),
         "b200msm_sum": (C.c_bool, [u32, vp, sz, sz, vp, sz]),
         "b200msm_batch_to_special": (C.c_bool, [u32, vp, sz, sz]),
+        "b200msm_batch_to_special_noalloc": (C.c_bool, [u32, vp, vp, sz, sz, vp]),
         "b200msm_batch_exp": (C.c_bool, [u32, sz, sz, C.POINTER(vp), sz, sz, vp, sz, sz, vp, sz]),
         "b200msm_debug_op": (C.c_bool, [u32, u32, vp, vp, vp, sz, sz]),
         "b200msm_set_option": (C.c_bool, [C.c_char_p, i64]),
@@ -323,6 +324,19 @@ def batch_to_special(group: int, points, inplace: bool = False) -> np.ndarray:
     if not load().b200msm_batch_to_special(group, _ptr(p), p.nbytes, n):
         _fail("b200msm_batch_to_special")
     return p
+
+
+NOALLOC_MAX_POINTS = 32768  # B200MSM_NOALLOC_MAX_POINTS
+
+
+def batch_to_special_noalloc_ptr(group: int, d_in: int, d_out: int, nbytes: int, n: int,
+                                 stream: int = 0) -> None:
+    """b200msm_batch_to_special_noalloc: batch_to_special on DEVICE pointers of the current
+    device with the scratch in the library's static device array (no cudaMalloc, no engine
+    context needed); enqueued on `stream` (a cudaStream_t handle), not synchronised.  At most
+    NOALLOC_MAX_POINTS per call; overlapping calls on one device race on the shared scratch."""
+    if not load().b200msm_batch_to_special_noalloc(group, d_in, d_out, nbytes, n, stream or None):
+        _fail("b200msm_batch_to_special_noalloc")
 
 
 # element-wise leaves (b200msm_debug_op)
