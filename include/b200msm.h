@@ -246,10 +246,14 @@ bool b200msm_stream_finish(uint64_t stream, void *out, size_t out_bytes);
  * group), "carry_segment" (carries per thread in the later accumulation rounds; 0 = 4),
  * "reduce_chunk" (log2 of the buckets per thread in the bucket reduction; 0 = automatic),
  * "num_gpus" (bound devices a call spreads over; 0 = all), "h2d_pack" (special-form bases leave
- * their constant Z behind on upload: 0 never, 1 pageable sources (default), 2 always),
+ * their constant Z behind on upload, packed to X|Y by host threads: 0 never (default: the plain
+ * copy measured faster on a 16-core host), 1 pageable sources, 2 always), "stage_lanes" (host
+ * threads / pinned lanes that stage pageable sources, 1..16, default 8), "h2d_taper" (the last
+ * upload ranges shrink again by this many growth steps per range; 0 = off, default),
  * "sort_overlap" (groups of windows whose counting sort runs under the previous group's
- * accumulation; 0 = automatic, 1 = one sort for all windows), "coop_accum" (lane-cooperative
- * bucket accumulation of the wide fields: 0 automatic, 1 off, 2 on). */
+ * accumulation; 0 = automatic = one sort for all windows, k > 1 = k groups), "coop_accum"
+ * (accumulation of the 24-limb field with the accumulator in shared-memory slots: 0 automatic =
+ * on, 1 off, 2 on). */
 bool b200msm_set_option(const char *name, int64_t value);
 /* CUDA-event timings (ms) of the phases of the most recent multi_exp on this thread's engine,
  * measured on the engine's own stream.  Writes up to `cap` values, returns how many phases exist.

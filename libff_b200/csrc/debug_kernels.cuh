@@ -14,8 +14,7 @@ enum DebugOp {
     DBG_FQ_INV = 5,
     DBG_FR_FROM_MONT = 6,
     DBG_FR_MUL = 7,
-    DBG_FQ_MUL_D = 8,  // the FP64-pipe product (fp_dfma.cuh); must equal DBG_FQ_MUL bit for bit
-    DBG_FR_MUL_D = 9,
+    // 8 and 9 were the FP64-pipe product (measured and rejected; now tools/fp64_product/)
     DBG_G_ADD = 10,
     DBG_G_DBL = 11,
     DBG_G_MADD = 12,   // b must be special (Z = 1) or zero
@@ -49,25 +48,22 @@ __global__ void k_debug_op(int op, const uint32_t *__restrict__ a, const uint32_
             const FC r = op == DBG_FQ_MUL_CALLED ? FC::mul(x, FC::load(b + (size_t)i * F::N)) : FC::sqr(x);
             r.store(out + (size_t)i * F::N);
         }
-    } else if (op <= DBG_FQ_INV || op == DBG_FQ_MUL_D || op == DBG_FQ_MUL2) {
+    } else if (op <= DBG_FQ_INV || op == DBG_FQ_MUL2) {
         F x = F::load(a + (size_t)i * F::N), y = F::zero(), r;
-        if (op <= DBG_FQ_MUL || op == DBG_FQ_MUL_D || op == DBG_FQ_MUL2) y = F::load(b + (size_t)i * F::N);
+        if (op <= DBG_FQ_MUL || op == DBG_FQ_MUL2) y = F::load(b + (size_t)i * F::N);
         switch (op) {
             case DBG_FQ_ADD: r = F::add(x, y); break;
             case DBG_FQ_SUB: r = F::sub(x, y); break;
             case DBG_FQ_MUL: r = F::mul(x, y); break;
-            case DBG_FQ_MUL_D: r = F::mul_d(x, y); break;
             case DBG_FQ_MUL2: r = F::mul2(x, y, F::add(x, y), F::sub(x, y)); break;
             case DBG_FQ_SQR: r = F::sqr(x); break;
             case DBG_FQ_NEG: r = F::neg(x); break;
             default: r = F::inv(x); break;
         }
         r.store(out + (size_t)i * F::N);
-    } else if (op == DBG_FR_FROM_MONT || op == DBG_FR_MUL || op == DBG_FR_MUL_D) {
+    } else if (op == DBG_FR_FROM_MONT || op == DBG_FR_MUL) {
         Fr x = Fr::load(a + (size_t)i * Fr::N);
-        Fr r = op == DBG_FR_MUL     ? Fr::mul(x, Fr::load(b + (size_t)i * Fr::N))
-               : op == DBG_FR_MUL_D ? Fr::mul_d(x, Fr::load(b + (size_t)i * Fr::N))
-                                    : Fr::from_mont(x);
+        Fr r = op == DBG_FR_MUL ? Fr::mul(x, Fr::load(b + (size_t)i * Fr::N)) : Fr::from_mont(x);
         r.store(out + (size_t)i * Fr::N);
     } else {
         F X1, Y1, Z1;

@@ -22,7 +22,6 @@
 #pragma once
 #include <cstdint>
 #include "field_params.cuh"
-#include "fp_dfma.cuh"
 
 namespace b200msm {
 
@@ -479,14 +478,6 @@ struct Fp {
     B200_DEV void sts(uint32_t *s, int stride) const {
 #pragma unroll
         for (int i = 0; i < N; i++) s[(size_t)i * stride] = v[i];
-    }
-
-    // The same product on the FP64 pipe (fp_dfma.cuh): identical canonical result, different
-    // execution unit -- call sites split their independent products between mul and mul_d.
-    B200_DEV static Fp mul_d(const Fp &a, const Fp &b) {
-        Fp t;
-        FpDfma<P>::mul_words(t.v, a.v, b.v);
-        return reduce_once(t);
     }
 
     // Montgomery -> plain integer (fp.tcc:270-281): one reduction of (a, 0, ..., 0)

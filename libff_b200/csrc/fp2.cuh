@@ -53,13 +53,6 @@ struct Fp2 {
         F s = F::mul(F::add(a.c0, a.c1), F::add(b.c0, b.c1));
         return Fp2{F::sub(v0, times_nr(v1)), F::sub(F::sub(s, v0), v1)};
     }
-    // the same with the three base-field products on the FP64 pipe (fp_dfma.cuh)
-    __device__ __noinline__ static Fp2 mul_d(Fp2 a, Fp2 b) {
-        F v0 = F::mul_d(a.c0, b.c0);
-        F v1 = F::mul_d(a.c1, b.c1);
-        F s = F::mul_d(F::add(a.c0, a.c1), F::add(b.c0, b.c1));
-        return Fp2{F::sub(v0, times_nr(v1)), F::sub(F::sub(s, v0), v1)};
-    }
     // a b + c d (no shared reduction in the extension: the base-field products already pair up)
     B200_DEV static Fp2 mul2(const Fp2 &a, const Fp2 &b, const Fp2 &c, const Fp2 &d) {
         return add(mul(a, b), mul(c, d));

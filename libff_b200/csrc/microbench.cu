@@ -12,6 +12,7 @@
 #include <cstdlib>
 
 #include "fp.cuh"
+#include "../../tools/fp64_product/fp_dfma.cuh"  // the rejected FP64-pipe product: measured here only
 
 using namespace b200msm;
 
@@ -170,6 +171,14 @@ __global__ void k_mont(uint32_t *out, uint32_t seed, int iters) {
     out[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
 
+// the Montgomery product on the FP64 pipe: same canonical result as Fp<P>::mul
+template <class P>
+__device__ __forceinline__ Fp<P> mul_fp64(const Fp<P> &a, const Fp<P> &b) {
+    Fp<P> t;
+    FpDfma<P>::mul_words(t.v, a.v, b.v);
+    return Fp<P>::reduce_once(t);
+}
+
 // NI integer-pipe products and ND FP64-pipe products (fp_dfma.cuh) per iteration on independent
 // chains: do the two multipliers of the SM add up?
 template <class P, int NI, int ND>
@@ -189,7 +198,7 @@ __global__ void k_mont_mix(uint32_t *out, uint32_t seed, int iters) {
 #pragma unroll
         for (int k = 0; k < NI; k++) x[k] = F::mul_inline(x[k], b);
 #pragma unroll
-        for (int k = 0; k < ND; k++) x[NI + k] = F::mul_d(x[NI + k], b);
+        for (int k = 0; k < ND; k++) x[NI + k] = mul_fp64<P>(x[NI + k], b);
     }
     uint32_t s = 0;
 #pragma unroll

@@ -1,6 +1,8 @@
 """GPU parity of the leaves of the path against the unmodified reference (SURVEY.md §8a rows
 a7-a13): Montgomery field arithmetic (fp.tcc:50-727, fp2.tcc:79-168), as_bigint, and the group law
 incl. its exceptional cases (test_groups.cpp:25-116 is the model: 0+0, 0+P, P+0, P+Q, P+P, P-P)."""
+import os
+
 import numpy as np
 import pytest
 
@@ -46,27 +48,17 @@ def test_coordinate_field_ops(engine, ref, gid):
                                   ref.field_op(fid, ref.OP_INV, nz))
 
 
-@pytest.mark.parametrize("gid", GROUPS)
-def test_fp64_pipe_product_equals_reference(engine, ref, gid):
-    """Fp::mul_d (the DFMA Montgomery product, fp_dfma.cuh) is the same function as mul_reduce
-    (fp.tcc:50-228): canonical output, bit for bit, incl. 0, 1, p-1 operands."""
-    fid = ref.FQ_OF_GROUP[gid]
-    n = 4099
-    a = rand_field(ref, fid, n, 11)
-    b = rand_field(ref, fid, n, 12)
-    a[0] = 0
-    b[1] = 0
-    b[2] = a[2]
-    minus_one = ref.field_op(fid, ref.OP_NEG, _one(ref, fid))
-    a[6], b[6], a[7] = minus_one[0], minus_one[0], minus_one[0]
-    b[8] = _one(ref, fid)[0]
-    np.testing.assert_array_equal(engine.debug_op(gid, engine.FQ_MUL_D, a, b),
-                                  ref.field_op(fid, ref.OP_MUL, a, b))
-    frid = ref.FR_OF_GROUP[gid]
-    s = rand_field(ref, frid, n, 13)
-    t = rand_field(ref, frid, n, 14)
-    np.testing.assert_array_equal(engine.debug_op(gid, engine.FR_MUL_D, s, t),
-                                  ref.field_op(frid, ref.OP_MUL, s, t))
+def test_fp64_pipe_product_equals_integer_product():
+    """The measured-and-rejected DFMA Montgomery product (tools/fp64_product/fp_dfma.cuh; not in
+    the library) still computes the same function as Fp::mul -- itself pinned to mul_reduce
+    (fp.tcc:50-228) by the test above -- for all seven moduli, bit for bit, incl. 0, 1, p-1."""
+    import subprocess
+    exe = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools",
+                       "fp64_product", "dfma_check")
+    if not os.path.exists(exe):
+        pytest.skip("tools/fp64_product/dfma_check not built (make -C libff_b200/csrc dfma_check)")
+    out = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0 and "dfma_check ok" in out.stdout, out.stdout + out.stderr
 
 
 @pytest.mark.parametrize("gid", GROUPS)
