@@ -119,16 +119,22 @@ using TailField = typename Rebind<F, ((!BaseLimbs<F>::EXT && BaseLimbs<F>::N >= 
 // The accumulation kernel inlines the products of 12-limb prime fields (calls cost 28.5 -> 37.8 ms
 // there) but calls them for the 12-limb quadratic extensions (38.3 -> 33.6 ms: three base-field
 // products per product no longer fit the instruction cache).
-// ... and rolls them (Fp::mul_rolled) where measured faster: bls12_377 Fq, whose fully unrolled
-// kernel is 171 KB and instruction-fetch bound (2^22: accumulation 28.9 -> 25.9 ms); the equally
-// wide bls12_381 Fq runs at 85 % of the pipe unrolled and loses 3 % rolled, so it stays unrolled.
+// ... and rolls them (Fp::mul_rolled) where measured faster.  r01 rolled bls12_377 Fq because its
+// unrolled kernel looked instruction-fetch bound (2^22: accumulation 28.9 -> 25.9 ms) while the
+// equally wide bls12_381 Fq ran at 85 % of the pipe unrolled.  The real cause was the lowering of
+// the reduction for moduli = 1 mod 2^32 (fp.cuh, ModTab): with p and INV read from constant
+// memory the unrolled product wins for bls12_377 as well (2^22: rolled 24.3, unrolled 22.9 ms;
+// Fq2 at 2^20: 27.0 -> 21.6 ms), so both 12-limb fields are unrolled now.
 template <class P>
 struct AccumRolled {
     static constexpr bool value = false;
 };
+#ifndef B200_ACCUM_ROLLED_377
+#define B200_ACCUM_ROLLED_377 0
+#endif
 template <>
 struct AccumRolled<Bls12377FqParams> {
-    static constexpr bool value = true;
+    static constexpr bool value = B200_ACCUM_ROLLED_377 != 0;
 };
 // bw6_761 Fq (24 limbs): the rolled inline product also beats the call, whose operands travel
 // through the stack (2^19: accumulation 30.5 -> 25.5 ms, stack frame 1792 -> 688 bytes).
