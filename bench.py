@@ -345,6 +345,12 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the MSM engine has no CPU path")
     torch.cuda.set_device(local)
+    # one process per GPU: run next to the GPU (first-touch placement of the pinned source and
+    # staging buffers, copy threads) -- libff_b200/numa.py; B200MSM_NO_NUMA=1 for the A/B
+    numa_info = {"bound": False, "why": "single process"}
+    if world > 1 and not os.environ.get("B200MSM_NO_NUMA"):
+        from libff_b200 import numa
+        numa_info = numa.bind_to_gpu_node(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     m.init(local)
@@ -491,7 +497,8 @@ def main():
                "h2d_bytes_per_step": n * (gb + sb) * world, "d2h_bytes_per_step": gb * world,
                "ms_per_step": dte / args.steps * 1e3,
                "ingest_ms": float(np.mean([p["ingest"] for p in ph_e])),
-               "call": "b200msm_multi_exp(host bases, host scalars) -> host result"}
+               "call": "b200msm_multi_exp(host bases, host scalars) -> host result",
+               "host_placement": numa_info}
 
         # the prover's shape: the bases (a proving key) stay resident, the scalars travel
         def step_rb():
