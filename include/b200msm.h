@@ -245,6 +245,8 @@ bool b200msm_stream_finish(uint64_t stream, void *out, size_t out_bytes);
  * the reduction of one group runs under the accumulation of the next; 0 = automatic, 1 = one
  * group), "carry_segment" (carries per thread in the later accumulation rounds; 0 = 4),
  * "reduce_chunk" (log2 of the buckets per thread in the bucket reduction; 0 = automatic),
+ * "reduce_cluster" (CTAs of the thread-block cluster one window's totals are spread over: 0 =
+ * automatic (up to 8), 1 = one CTA per window),
  * "num_gpus" (bound devices a call spreads over; 0 = all), "h2d_pack" (special-form bases leave
  * their constant Z behind on upload, packed to X|Y by host threads: 0 never (default: the plain
  * copy measured faster on a 16-core host), 1 pageable sources, 2 always), "stage_lanes" (host

@@ -42,6 +42,7 @@ bool Ctx::reserve(Slot s, size_t bytes, void **out) {
             B200_CUDA(cudaStreamSynchronize(tail_stream));
             B200_CUDA(cudaStreamSynchronize(acc_stream));
             B200_CUDA(cudaStreamSynchronize(copy_stream));
+            if (sort_stream) B200_CUDA(cudaStreamSynchronize(sort_stream));
             B200_CUDA(cudaFree(slot_ptr[s]));
             slot_ptr[s] = nullptr;
             slot_bytes[s] = 0;
@@ -1646,6 +1647,7 @@ bool b200msm_set_option(const char *name, int64_t value) {
         {"window_groups", &Ctx::opt_window_groups, 0, 64},
         {"carry_segment", &Ctx::opt_carry_segment, 0, 1024},
         {"reduce_chunk", &Ctx::opt_reduce_chunk, 0, 12},
+        {"reduce_cluster", &Ctx::opt_reduce_cluster, 0, 8},
         {"h2d_growth", &Ctx::opt_h2d_growth, 0, 400},
         {"trace", &Ctx::opt_trace, 0, 1},
         {"h2d_shared_buckets", &Ctx::opt_h2d_shared_buckets, 0, 1},

@@ -153,6 +153,7 @@ struct Ctx {
     int opt_window_groups = 0; // groups the windows are walked in (top-down); 0 = automatic, 1 = one
     int opt_carry_segment = 0; // carries per thread in the later accumulation rounds; 0 = automatic
     int opt_reduce_chunk = 0; // log2 of the buckets per thread in the reduction; 0 = automatic
+    int opt_reduce_cluster = 0; // CTAs (SMs) one window's totals are spread over; 0 = automatic (up to 8), 1 = one
     // special-form bases leave Z behind on upload: 0 never (default: measured, the host-side packing
     // loses to the plain copy on a 16-core host, profiles/pack_sweep_r02.log), 1 pageable sources, 2 always
     int opt_h2d_pack = 0;

@@ -376,9 +376,14 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
     if (pre) window_T = windows + (size_t)Wr_max * R::XW;
     constexpr int WR_THREADS = 256;
     const size_t wr_smem = (size_t)WR_THREADS * R::XW * 4;
+    // the same kernel spread over a cluster of CTAs (one warp per scheduler on each SM)
+    constexpr int WR_CL_THREADS = 128;
+    const size_t wr_cl_smem = (size_t)WR_CL_THREADS * R::XW * 4;
     if (!(ctx.attr_mask & (1u << C::ID))) {  // function attributes are per device
         B200_CUDA(cudaFuncSetAttribute(k_window_reduce<C, WR_THREADS>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wr_smem));
+        B200_CUDA(cudaFuncSetAttribute(k_window_reduce<C, WR_CL_THREADS>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wr_cl_smem));
         if (!attr_accum_sm<C>()) return false;
         ctx.attr_mask |= 1u << C::ID;
     }
@@ -601,9 +606,31 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
         B200_CUDA(cudaEventRecord(ctx.ev_tail_go, st));
         B200_CUDA(cudaStreamWaitEvent(fs, ctx.ev_tail_go, 0));
     }
-    k_window_reduce<C, WR_THREADS><<<Wr, WR_THREADS, wr_smem, fs>>>(chunks, chunk_T, nchunks, log2K, 0u,
-                                                                    windows, window_T);
-    B200_LAUNCH_CHECK(ctx);
+    // CTAs per window: as many as still give every thread a chunk, at most 8 (portable cluster size)
+    unsigned wr_cl = ctx.opt_reduce_cluster > 0 ? (unsigned)ctx.opt_reduce_cluster : 8u;
+    while (wr_cl > 1 && (size_t)wr_cl * WR_CL_THREADS > std::max<size_t>(nchunks, WR_THREADS)) wr_cl >>= 1;
+    if (wr_cl > 1) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)Wr * wr_cl);
+        cfg.blockDim = dim3(WR_CL_THREADS);
+        cfg.dynamicSmemBytes = wr_cl_smem;
+        cfg.stream = fs;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = wr_cl;
+        at[0].val.clusterDim.y = 1;
+        at[0].val.clusterDim.z = 1;
+        cfg.attrs = at;
+        cfg.numAttrs = 1;
+        B200_CUDA(cudaLaunchKernelEx(&cfg, k_window_reduce<C, WR_CL_THREADS>, (const uint32_t *)chunks,
+                                     (const uint32_t *)chunk_T, (uint32_t)nchunks, (uint32_t)log2K, 0u,
+                                     windows, window_T));
+        ctx.launches++;
+    } else {
+        k_window_reduce<C, WR_THREADS><<<Wr, WR_THREADS, wr_smem, fs>>>(chunks, chunk_T, nchunks, log2K, 0u,
+                                                                        windows, window_T);
+        B200_LAUNCH_CHECK(ctx);
+    }
     if (pre)
         k_final_slices<C><<<1, 32, 0, fs>>>(windows, window_T, (int)V, (int)log2Br, (uint32_t *)d_out);
     else

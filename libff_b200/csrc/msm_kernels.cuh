@@ -17,6 +17,8 @@
 //   k_final         Horner over windows (multiexp.tcc:309-314) -> reference coordinates
 // Any bucket-method schedule yields the same group element; parity is on the affine result.
 #pragma once
+#include <cooperative_groups.h>
+
 #include "curves.cuh"
 #include "fp_coop.cuh"
 
@@ -745,6 +747,10 @@ __global__ void __launch_bounds__(64)
 // A_t = sum_j (j - tQ) T_j over its chunks.  The remaining weights t < THREADS are applied with a
 // short double-and-add in parallel; K and Q are powers of two, i.e. doublings.  A shared-memory
 // tree then adds the THREADS partial results.
+// A window may be spread over the CTAs of a thread-block CLUSTER (launch attribute; CL = 1 for a
+// plain launch): 8 warps of dependent product chains on ONE SM queue for its multiply pipe while
+// the other SMs idle, so CL x THREADS threads on CL SMs walk shorter chains without sharing a
+// pipe, and CTA 0 collects the CL partial results through distributed shared memory.
 template <class C, int THREADS>
 __global__ void __launch_bounds__(THREADS)
     k_window_reduce(const uint32_t *__restrict__ chunk_L, const uint32_t *__restrict__ chunk_T,
@@ -754,8 +760,12 @@ __global__ void __launch_bounds__(THREADS)
     using F = TailField<typename C::Fq>;
     using X = XYZZ<F>;
     extern __shared__ uint32_t smem[];
-    const uint32_t w = w0 + blockIdx.x, t = threadIdx.x;
-    const uint32_t Q = chunks > (uint32_t)THREADS ? chunks / THREADS : 1u;
+    cooperative_groups::cluster_group cluster = cooperative_groups::this_cluster();
+    const uint32_t CL = cluster.num_blocks(), rank = cluster.block_rank();
+    const uint32_t lt = threadIdx.x;                  // thread inside its CTA
+    const uint32_t w = w0 + blockIdx.x / CL, t = rank * THREADS + lt;  // thread inside the window
+    const uint32_t TT = (uint32_t)THREADS * CL;
+    const uint32_t Q = chunks > TT ? chunks / TT : 1u;
     const uint32_t log2Q = 31 - __clz(Q);
     X total = X::inf(), plain = X::inf();
     if (t * Q < chunks) {
@@ -797,31 +807,43 @@ __global__ void __launch_bounds__(THREADS)
         total = sumL;
         X::add(total, y);
     }
-    total.store(smem + (size_t)t * R::XW);
-    __syncthreads();
-    for (uint32_t d = THREADS / 2; d > 0; d >>= 1) {
-        if (t < d) {
-            X q = X::load(smem + (size_t)(t + d) * R::XW);
-            X::add(total, q);
-            total.store(smem + (size_t)t * R::XW);
-        }
+    // sum over the threads of the CTA (shared-memory tree), then over the CTAs of the cluster
+    auto reduce = [&](X &val) {
+        val.store(smem + (size_t)lt * R::XW);
         __syncthreads();
-    }
-    if (t == 0) total.store(window_sums + (size_t)w * R::XW);
-    if (window_totals == nullptr) return;  // uniform across the block
+        for (uint32_t d = THREADS / 2; d > 0; d >>= 1) {
+            if (lt < d) {
+                X q = X::load(smem + (size_t)(lt + d) * R::XW);
+                X::add(val, q);
+                val.store(smem + (size_t)lt * R::XW);
+            }
+            __syncthreads();
+        }
+        if (CL > 1) {
+            cluster.sync();  // slot 0 of every CTA holds that CTA's partial result
+            if (rank == 0 && lt > 0 && lt < CL) {
+                val = X::load(cluster.map_shared_rank(smem, lt));
+                val.store(smem + (size_t)lt * R::XW);
+            }
+            __syncthreads();
+            for (uint32_t d = CL / 2; d > 0; d >>= 1) {
+                if (rank == 0 && lt < d) {
+                    X q = X::load(smem + (size_t)(lt + d) * R::XW);
+                    X::add(val, q);
+                    val.store(smem + (size_t)lt * R::XW);
+                }
+                __syncthreads();
+            }
+            cluster.sync();  // remote shared memory must outlive the reads above
+        }
+    };
+    reduce(total);
+    if (rank == 0 && lt == 0) total.store(window_sums + (size_t)w * R::XW);
+    if (window_totals == nullptr) return;  // uniform across the cluster
     // the unweighted sum of the window's buckets (used when one bucket set is cut into slices)
     __syncthreads();
-    plain.store(smem + (size_t)t * R::XW);
-    __syncthreads();
-    for (uint32_t d = THREADS / 2; d > 0; d >>= 1) {
-        if (t < d) {
-            X q = X::load(smem + (size_t)(t + d) * R::XW);
-            X::add(plain, q);
-            plain.store(smem + (size_t)t * R::XW);
-        }
-        __syncthreads();
-    }
-    if (t == 0) plain.store(window_totals + (size_t)w * R::XW);
+    reduce(plain);
+    if (rank == 0 && lt == 0) plain.store(window_totals + (size_t)w * R::XW);
 }
 
 // One doubling shared by the lanes of a warp.  The c doublings between windows are a serial

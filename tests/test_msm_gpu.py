@@ -253,6 +253,26 @@ def test_multi_exp_segment_lengths(engine, ref, seg):
         engine.set_option("window_bits", 0)
 
 
+@pytest.mark.parametrize("gid", [0, 1, 2, 3])
+def test_window_totals_over_a_cluster(engine, ref, gid):
+    """The per-window totals run on one CTA or spread over a thread-block cluster of 2 / 4 / 8 CTAs
+    that combine through distributed shared memory (option reduce_cluster; 0 = automatic): same
+    element for every setting, for digit sizes that give fewer chunks than threads and more."""
+    n = 5000 if gid != 3 else 900
+    bases = ref.gen_bases_walk(gid, n)
+    scalars = ref.gen_scalars(gid, n, start=21)
+    want = ref.multi_exp(gid, bases, scalars)
+    try:
+        for cbits in (0, 7, 14, 16):
+            engine.set_option("window_bits", cbits)
+            for cl in (1, 2, 4, 8, 0):
+                engine.set_option("reduce_cluster", cl)
+                assert_same_point(ref, gid, engine.multi_exp(gid, bases, scalars), want)
+    finally:
+        engine.set_option("reduce_cluster", 0)
+        engine.set_option("window_bits", 0)
+
+
 @pytest.mark.parametrize("gid", GROUPS)
 @pytest.mark.parametrize("shared", [1, 0])
 @pytest.mark.parametrize("parts", [1, 2, 3, 7])
