@@ -394,11 +394,19 @@ __global__ void __launch_bounds__(128, Raw<C>::XW <= 32 ? 4 : 1)
 #ifndef B200_SM_MINBLOCKS
 #define B200_SM_MINBLOCKS 4
 #endif
+#ifndef B200_SM_MIN_LIMBS
+#define B200_SM_MIN_LIMBS 24
+#endif
+#ifndef B200_SM_MINBLOCKS_12
+#define B200_SM_MINBLOCKS_12 8
+#endif
 template <class C>
 struct SmemAccum {
-    static constexpr bool value = !BaseLimbs<typename C::Fq>::EXT && BaseLimbs<typename C::Fq>::N >= 24;
+    static constexpr bool value =
+        !BaseLimbs<typename C::Fq>::EXT && BaseLimbs<typename C::Fq>::N >= B200_SM_MIN_LIMBS;
     static constexpr int SLOTS = 8;
     static constexpr int THREADS = B200_SM_THREADS;
+    static constexpr int MINBLOCKS = BaseLimbs<typename C::Fq>::N >= 24 ? B200_SM_MINBLOCKS : B200_SM_MINBLOCKS_12;
     static constexpr size_t BYTES = (size_t)SLOTS * BaseLimbs<typename C::Fq>::N * THREADS * 4;
 };
 
@@ -576,7 +584,7 @@ struct SmemXYZZ {
 };
 
 template <class C>
-__global__ void __launch_bounds__(SmemAccum<C>::THREADS, B200_SM_MINBLOCKS)
+__global__ void __launch_bounds__(SmemAccum<C>::THREADS, SmemAccum<C>::MINBLOCKS)
     k_accum_first_sm(const Entry *__restrict__ sorted, const uint32_t *__restrict__ offsets,
                      const uint32_t *__restrict__ seg_bucket, uint32_t total, uint32_t SEG,
                      uint32_t t_begin, uint32_t t_end, const uint32_t *__restrict__ aff,
