@@ -25,7 +25,7 @@ def visible_gpus():
     return torch.cuda.device_count()
 
 
-@pytest.fixture(scope="module", params=[2, 3])
+@pytest.fixture(scope="module", params=[2, 3, 8])
 def multi(request, engine):
     """the engine bound to `param` contexts: distinct GPUs where the box has them"""
     want = request.param
@@ -92,6 +92,27 @@ def test_every_device_takes_its_range(multi, ref):
         engine.set_option("num_gpus", 0)
     with pytest.raises(engine.B200MsmError, match="num_gpus"):
         engine.set_option("num_gpus", D + 1)
+    rb.release()
+    rs.release()
+
+
+def test_sharded_result_equals_closed_form_at_2p22(multi, ref):
+    """2^22 alt_bn128 G1 points cut over the bound devices (2, 3 -- an uneven split -- and 8):
+    the combined point equals (sum s_i (a + i d)) G computed with numpy / Python integers and ONE
+    reference scalar multiplication, for resident inputs, host buffers and resident bases."""
+    engine, D = multi
+    gid, n = 0, 1 << 22
+    g = pm.GROUPS[gid]
+    ref.lib().ref_set_num_threads(max(1, len(os.sched_getaffinity(0))))
+    bases = ref.gen_bases_walk(gid, n)
+    scalars = ref.gen_scalars(gid, n)
+    k = pm.walk_expected_scalar_fast(g, scalars)
+    want = ref.scalar_mul(gid, ref.group_constants(gid)[1], g.encode_scalars([k])[0])
+    rb, rs = engine.ResidentBases(gid, bases), engine.ResidentScalars(gid, scalars)
+    np.testing.assert_array_equal(affine(ref, gid, engine.multi_exp_resident(rb, rs)), want)
+    assert all(engine.device_timings(d).get("total", 0.0) > 0 for d in range(D))
+    np.testing.assert_array_equal(affine(ref, gid, engine.multi_exp_resident_bases(rb, scalars)), want)
+    np.testing.assert_array_equal(affine(ref, gid, engine.multi_exp(gid, bases, scalars)), want)
     rb.release()
     rs.release()
 
