@@ -342,7 +342,7 @@ def batch_to_special_noalloc_ptr(group: int, d_in: int, d_out: int, nbytes: int,
 # element-wise leaves (b200msm_debug_op)
 FQ_ADD, FQ_SUB, FQ_MUL, FQ_SQR, FQ_NEG, FQ_INV, FR_FROM_MONT, FR_MUL = range(8)
 G_ADD, G_DBL, G_MADD, G_NEG, FQ_MUL2 = 10, 11, 12, 13, 14
-FQ_MUL_ROLLED, FQ_MUL2_ROLLED, FQ_MUL_CALLED, FQ_SQR_CALLED = 15, 16, 17, 18
+FQ_MUL_ROLLED, FQ_MUL2_ROLLED, FQ_MUL_CALLED, FQ_SQR_CALLED, FQ_MUL_SEPARATED = 15, 16, 17, 18, 19
 
 
 def debug_op(group: int, op: int, a, b=None) -> np.ndarray:

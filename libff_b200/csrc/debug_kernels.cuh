@@ -25,6 +25,9 @@ enum DebugOp {
     DBG_FQ_MUL2_ROLLED = 16,
     DBG_FQ_MUL_CALLED = 17,
     DBG_FQ_SQR_CALLED = 18,
+    // plain integer product + separate Montgomery reduction (the halves of the lazy Fq2 product),
+    // on the base prime field of the group
+    DBG_FQ_MUL_SEPARATED = 19,
 };
 
 template <class C>
@@ -36,7 +39,14 @@ __global__ void k_debug_op(int op, const uint32_t *__restrict__ a, const uint32_
     using X = XYZZ<F>;
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    if (op >= DBG_FQ_MUL_ROLLED && op <= DBG_FQ_SQR_CALLED) {
+    if (op == DBG_FQ_MUL_SEPARATED) {
+        using B = typename BaseField<F>::type;  // N words per element of the base prime field
+        constexpr int per = F::N / B::N;        // 1, or 2 for a quadratic extension: both halves
+        for (int h = 0; h < per; h++) {
+            const B x = B::load(a + (size_t)i * F::N + h * B::N), y = B::load(b + (size_t)i * F::N + h * B::N);
+            B::mul_separated(x, y).store(out + (size_t)i * F::N + h * B::N);
+        }
+    } else if (op >= DBG_FQ_MUL_ROLLED && op <= DBG_FQ_SQR_CALLED) {
         using FR = typename Rebind<F, -1>::type;  // every product rolled
         using FC = typename Rebind<F, 1>::type;   // every product a call
         if (op == DBG_FQ_MUL_ROLLED || op == DBG_FQ_MUL2_ROLLED) {

@@ -763,7 +763,7 @@ template <class C>
 size_t debug_elem_bytes_impl(int op) {
     using R = Raw<C>;
     if (op <= DBG_FQ_INV || op == DBG_FQ_MUL2 ||
-        (op >= DBG_FQ_MUL_ROLLED && op <= DBG_FQ_SQR_CALLED))
+        (op >= DBG_FQ_MUL_ROLLED && op <= DBG_FQ_MUL_SEPARATED))
         return (size_t)R::CW * 4;
     if (op == DBG_FR_FROM_MONT || op == DBG_FR_MUL) return (size_t)R::SW * 4;
     if (op >= DBG_G_ADD && op <= DBG_G_NEG) return (size_t)R::PW * 4;

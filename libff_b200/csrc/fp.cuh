@@ -345,6 +345,110 @@ struct Fp {
         return reduce_once(t);
     }
 
+    // ---- separated product and reduction (lazy reduction in the quadratic extension, fp2.cuh) ----
+    // One row of the plain integer product: T += a*bi, no reduction.  The caller takes the finished
+    // low limb E[0] after every row; the one-limb shift is the same role swap as in mont_row.
+    B200_DEV static void wide_row(uint32_t *E, uint32_t *O, const uint32_t *a, uint32_t bi, bool first) {
+        if (first) {
+            limb::row_set<N>(O, a + 1, bi);
+            limb::row_set<N>(E, a, bi);
+        } else {
+            asm volatile("add.cc.u32 %0, %0, %1;" : "+r"(E[0]) : "r"(O[1]));
+            limb::row_acc_shift<N>(O, a + 1, bi);
+            limb::row_acc<N>(E, a, bi);
+            asm volatile("addc.u32 %0, %0, 0;" : "+r"(O[N - 1]));
+        }
+    }
+    // T[0 .. 2N) = a * b as integers, any a, b < 2^(32 N) (e.g. unreduced sums of two elements)
+    B200_DEV static void mul_wide(uint32_t *T, const uint32_t *a, const uint32_t *b) {
+        uint32_t E[N], O[N];
+#pragma unroll
+        for (int i = 0; i < N; i += 2) {
+            wide_row(E, O, a, b[i], i == 0);
+            T[i] = E[0];
+            wide_row(O, E, a, b[i + 1], false);
+            T[i + 1] = O[0];
+        }
+        asm volatile("add.cc.u32 %0, %1, %2;" : "=r"(T[N]) : "r"(E[0]), "r"(O[1]));
+#pragma unroll
+        for (int i = 1; i < N - 1; i++)
+            asm volatile("addc.cc.u32 %0, %1, %2;" : "=r"(T[N + i]) : "r"(E[i]), "r"(O[i + 1]));
+        asm volatile("addc.u32 %0, %1, 0;" : "=r"(T[2 * N - 1]) : "r"(E[N - 1]));
+    }
+    // One row of a reduction without a product: m = T[0]*INV; T = (T + m*p) >> 32.  The shift of
+    // the previous row is folded into this row's multiply-adds (acc[j] = p*m + acc[j+2]).
+    B200_DEV static void redc_row(uint32_t *E, uint32_t *O, bool first) {
+        uint32_t mod[N];
+#pragma unroll
+        for (int i = 0; i < N; i++) mod[i] = HIDE_MOD ? c_modtab<P>.v[i] : P::mod(i);
+        const uint32_t inv = HIDE_MOD ? c_modtab<P>.inv : P::INV;
+        if (first) {
+            const uint32_t m = E[0] * inv;
+            limb::row_set<N>(O, mod + 1, m);
+            limb::row_acc<N>(E, mod, m);
+            asm volatile("addc.u32 %0, %0, 0;" : "+r"(O[N - 1]));
+        } else {
+            asm volatile("add.cc.u32 %0, %0, %1;" : "+r"(E[0]) : "r"(O[1]));
+            const uint32_t m = E[0] * inv;  // mul.lo leaves the carry flag alone
+            limb::row_acc_shift<N>(O, mod + 1, m);
+            limb::row_acc<N>(E, mod, m);
+            asm volatile("addc.u32 %0, %0, 0;" : "+r"(O[N - 1]));
+        }
+    }
+    // T / R mod p, canonical, for 0 <= T < p R given as 2N limbs: N reduction rows on the low
+    // half (their value ends <= p), plus the high half (< p), one conditional subtraction.
+    B200_DEV static Fp redc_wide(const uint32_t *T) {
+        uint32_t E[N], O[N];
+#pragma unroll
+        for (int i = 0; i < N; i++) E[i] = T[i];
+#pragma unroll
+        for (int i = 0; i < N; i += 2) {
+            redc_row(E, O, i == 0);
+            redc_row(O, E, false);
+        }
+        Fp t;
+        asm volatile("add.cc.u32 %0, %1, %2;" : "=r"(t.v[0]) : "r"(E[0]), "r"(O[1]));
+#pragma unroll
+        for (int i = 1; i < N - 1; i++)
+            asm volatile("addc.cc.u32 %0, %1, %2;" : "=r"(t.v[i]) : "r"(E[i]), "r"(O[i + 1]));
+        asm volatile("addc.u32 %0, %1, 0;" : "=r"(t.v[N - 1]) : "r"(E[N - 1]));
+        asm volatile("add.cc.u32 %0, %0, %1;" : "+r"(t.v[0]) : "r"(T[N]));
+#pragma unroll
+        for (int i = 1; i < N - 1; i++) asm volatile("addc.cc.u32 %0, %0, %1;" : "+r"(t.v[i]) : "r"(T[N + i]));
+        asm volatile("addc.u32 %0, %0, %1;" : "+r"(t.v[N - 1]) : "r"(T[2 * N - 1]));
+        return reduce_once(t);
+    }
+    // a + b as integers (no reduction; canonical a, b: the sum fits, the top limb has spare bits)
+    B200_DEV static void add_plain(uint32_t *r, const uint32_t *a, const uint32_t *b) {
+        asm volatile("add.cc.u32 %0, %1, %2;" : "=r"(r[0]) : "r"(a[0]), "r"(b[0]));
+#pragma unroll
+        for (int i = 1; i < N - 1; i++) asm volatile("addc.cc.u32 %0, %1, %2;" : "=r"(r[i]) : "r"(a[i]), "r"(b[i]));
+        asm volatile("addc.u32 %0, %1, %2;" : "=r"(r[N - 1]) : "r"(a[N - 1]), "r"(b[N - 1]));
+    }
+    // X -= Y over 2N limbs; returns the borrow as a mask (0 or 0xffffffff)
+    B200_DEV static uint32_t wide_sub(uint32_t *X, const uint32_t *Y) {
+        asm volatile("sub.cc.u32 %0, %0, %1;" : "+r"(X[0]) : "r"(Y[0]));
+#pragma unroll
+        for (int i = 1; i < 2 * N; i++) asm volatile("subc.cc.u32 %0, %0, %1;" : "+r"(X[i]) : "r"(Y[i]));
+        uint32_t borrow;
+        asm volatile("subc.u32 %0, 0, 0;" : "=r"(borrow));
+        return borrow;
+    }
+    // X += (p & mask) * R: brings a difference of two products in (-p R, 0) back into [0, p R)
+    B200_DEV static void wide_add_pR(uint32_t *X, uint32_t mask) {
+        asm volatile("add.cc.u32 %0, %0, %1;" : "+r"(X[N]) : "r"(P::mod(0) & mask));
+#pragma unroll
+        for (int i = 1; i < N - 1; i++)
+            asm volatile("addc.cc.u32 %0, %0, %1;" : "+r"(X[N + i]) : "r"(P::mod(i) & mask));
+        asm volatile("addc.u32 %0, %0, %1;" : "+r"(X[2 * N - 1]) : "r"(P::mod(N - 1) & mask));
+    }
+    // the same function as mul through the separated form (parity tests of the two halves)
+    B200_DEV static Fp mul_separated(const Fp &a, const Fp &b) {
+        uint32_t T[2 * N];
+        mul_wide(T, a.v, b.v);
+        return redc_wide(T);
+    }
+
     // fp.tcc:50-228: a*b*R^-1 mod p, canonical.  Wide fields call one shared copy of the
     // product (a 24-limb product is ~1300 instructions; inlining a dozen per group operation
     // only thrashes the instruction cache and the compiler).

@@ -113,6 +113,58 @@ def test_product_code_shapes_agree(engine, ref, gid):
     np.testing.assert_array_equal(engine.debug_op(gid, engine.FQ_MUL2_ROLLED, a, b), want2)
 
 
+BASE_GROUP = {0: 0, 1: 0, 2: 2, 3: 3, 4: 2, 5: 3, 6: 6, 7: 6}  # a group whose Fq is the base prime field
+
+
+@pytest.mark.parametrize("gid", GROUPS)
+def test_separated_product_and_reduction(engine, ref, gid):
+    """Fp::mul_wide (plain 2N-limb integer product) followed by Fp::redc_wide (Montgomery reduction
+    of a double-width value) -- the halves the lazy-reduction Fq2 product is built from -- give the
+    reference's product (fp.tcc:50-228) on the base prime field, incl. 0, 1, p-1 operands."""
+    fid = ref.FQ_OF_GROUP[gid]
+    bfid = ref.FQ_OF_GROUP[BASE_GROUP[gid]]
+    w = ref.lib().ref_field_bytes(bfid) // 8
+    n = 1025
+    a = rand_field(ref, fid, n, 41)
+    b = rand_field(ref, fid, n, 42)
+    minus_one = ref.field_op(bfid, ref.OP_NEG, _one(ref, bfid))[0]
+    a2, b2 = a.reshape(-1, w), b.reshape(-1, w)
+    a2[0] = 0
+    b2[1] = 0
+    a2[2], b2[2] = minus_one, minus_one
+    a2[3], b2[3] = minus_one, _one(ref, bfid)[0]
+    got = engine.debug_op(gid, engine.FQ_MUL_SEPARATED, a2.reshape(a.shape), b2.reshape(b.shape))
+    np.testing.assert_array_equal(got.reshape(-1, w), ref.field_op(bfid, ref.OP_MUL, a2, b2))
+
+
+@pytest.mark.parametrize("gid", [1, 4, 7])
+def test_lazy_fq2_product_corner_values(engine, ref, gid):
+    """The lazy-reduction Fq2 product (fp2.cuh mul_lazy: differences of unreduced products, p R added
+    back on a borrow, five-fold for bls12_377's non-residue) on coordinates 0, 1 and p - 1 in every
+    combination, against Fp2_model::operator* (fp2.tcc:101-114)."""
+    fid = ref.FQ_OF_GROUP[gid]
+    bfid = ref.FQ_OF_GROUP[BASE_GROUP[gid]]
+    w = ref.lib().ref_field_bytes(bfid) // 8
+    one = _one(ref, bfid)[0]
+    minus_one = ref.field_op(bfid, ref.OP_NEG, _one(ref, bfid))[0]
+    vals = [np.zeros(w, dtype=np.uint64), one, minus_one, rand_field(ref, bfid, 1, 5)[0]]
+    rows_a, rows_b = [], []
+    for x0 in vals:
+        for x1 in vals:
+            for y0 in vals:
+                for y1 in vals:
+                    rows_a.append(np.concatenate([x0, x1]))
+                    rows_b.append(np.concatenate([y0, y1]))
+    a, b = np.array(rows_a, dtype=np.uint64), np.array(rows_b, dtype=np.uint64)
+    prod = ref.field_op(fid, ref.OP_MUL, a, b)
+    np.testing.assert_array_equal(engine.debug_op(gid, engine.FQ_MUL, a, b), prod)
+    # a b + (a + b)(a - b) through the two-product form that shares its reductions (mul2_lazy)
+    want2 = ref.field_op(fid, ref.OP_ADD, prod,
+                         ref.field_op(fid, ref.OP_MUL, ref.field_op(fid, ref.OP_ADD, a, b),
+                                      ref.field_op(fid, ref.OP_SUB, a, b)))
+    np.testing.assert_array_equal(engine.debug_op(gid, engine.FQ_MUL2, a, b), want2)
+
+
 def _one(ref, fid):
     """Montgomery one of field fid as a (1, words) array (Fq2: (1, 0))."""
     words = ref.lib().ref_field_bytes(fid) // 8
