@@ -13,6 +13,7 @@ run bench_${TAG}_alt_bn128_g2_2p20 --group alt_bn128_g2 --log2n 20 --no-cpu-base
 run bench_${TAG}_bw6_761_g1_2p19 --group bw6_761_g1 --log2n 19 --no-cpu-baseline
 run bench_${TAG}_bls12_377_g2_2p20 --group bls12_377_g2 --log2n 20 --no-cpu-baseline
 run bench_${TAG}_bls12_381_g1_2p22 --group bls12_381_g1 --log2n 22 --no-cpu-baseline
+run bench_${TAG}_bls12_381_g2_2p20 --group bls12_381_g2 --log2n 20 --no-cpu-baseline
 run bench_${TAG}_batch_exp --op batch_exp
 run bench_${TAG}_batch_to_special --op batch_to_special
 run bench_${TAG}_reference --impl reference --steps 2 --warmup 1
