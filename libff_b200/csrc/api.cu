@@ -254,27 +254,48 @@ bool run_msm(Ctx &ctx, const GroupOps *ops, const void *d_aff, const uint8_t *d_
 
 // How many point ranges a host-buffer multi_exp is cut into so that the upload of range k + 1
 // overlaps the computation of range k.
-size_t pick_parts(const Ctx &ctx, size_t n, bool scalars_only) {
+// Ranges of a pipelined call.  What a call pays on top of max(upload, computation) is the first
+// range's upload, the last range's computation and a cost per range (its sort launches, sparser
+// buckets in the merging accumulation), so the best count grows like the square root of the
+// call's length.  Measured per field class (profiles/e2e_ranges_r02d.log): the 8-limb prime field
+// gains from 2^19 points on; the merging accumulation of the wider fields is a slower kernel than
+// their plain one (the 24-limb field's is not the shared-memory slot kernel), so they take fewer
+// ranges and bw6_761 none.
+size_t pick_parts(const Ctx &ctx, const GroupOps *ops, size_t n, bool scalars_only) {
     if (scalars_only && ctx.opt_h2d_parts == 0) {
         // a quarter of the bytes: few ranges, so that the buckets stay dense in every range
         return n < ((size_t)1 << 21) ? 1 : 4;
     }
     if (ctx.opt_h2d_parts > 0) return std::min<size_t>((size_t)ctx.opt_h2d_parts, std::max<size_t>(n, 1));
-    if (n < ((size_t)1 << 21)) return 1;
+    const bool prime8 = ops->affine_bytes == 64;                           // alt_bn128 G1
+    const bool prime24 = ops->affine_bytes == 192 && ops->scalar_bytes == 48;  // bw6_761
+    if (prime24) return 1;
+    if (!ctx.opt_h2d_shared_buckets) return n < ((size_t)1 << 21) ? 1 : n < ((size_t)1 << 23) ? 3 : 5;
+    if (prime8) {
+        if (n < ((size_t)1 << 19)) return 1;
+        if (n < ((size_t)1 << 20)) return 2;
+        if (n < ((size_t)1 << 22)) return 4;
+        if (n < ((size_t)1 << 24)) return 8;
+        if (n < ((size_t)1 << 25)) return 12;
+        return 16;
+    }
+    if (n < ((size_t)1 << 20)) return 1;
     if (n < ((size_t)1 << 22)) return 2;
     if (n < ((size_t)1 << 23)) return 3;
-    // shared buckets: no per-range reduction, so more and shorter ranges pay (measured at 2^24:
-    // 12 ranges growing by 1.2x, profiles/e2e_sweep_r01e.log)
-    return ctx.opt_h2d_shared_buckets ? 12 : 5;
+    return 6;
 }
 
 // Range boundaries of a pipelined call: sizes grow geometrically (x h2d_growth %, default 1.3),
 // so the first upload -- the only one nothing overlaps -- is short, while the later, longer MSMs
 // still finish after their successor's upload.  bounds has parts + 1 entries.
 void pick_bounds(const Ctx &ctx, size_t n, size_t parts, size_t *bounds, bool scalars_only) {
+    // With the computation as fast as the upload the LAST range's computation is as exposed as
+    // the first range's upload: long calls use (nearly) equal ranges (2^24: 12 x 1.2 51.0 ms,
+    // 12 x 1.1 49.3; 2^26: 16 x 1.2 186 ms, 16 equal 169 ms)
     const double g = ctx.opt_h2d_growth > 0 ? ctx.opt_h2d_growth / 100.0
                      : scalars_only ? 2.0
-                     : (ctx.opt_h2d_shared_buckets && parts > 5) ? 1.2 : 1.3;
+                     : !ctx.opt_h2d_shared_buckets ? 1.3
+                     : parts >= 16 ? 1.0 : parts >= 12 ? 1.1 : parts > 5 ? 1.2 : 1.3;
     // weights: geometric growth from the first range; with h2d_taper the trailing ranges shrink
     // again (the last range's computation overlaps no upload either)
     auto weight = [&](size_t k) {
@@ -486,7 +507,7 @@ bool msm_host_on(Ctx &ctx, const GroupOps *ops, const void *bases, const void *d
     }
     if (!ctx.reserve(SL_SCALARS, n * sb, &d_sc)) return false;
     if (!ctx.reserve(SL_OUT, gb, &d_out)) return false;
-    size_t parts = pick_parts(ctx, n, resident);
+    size_t parts = pick_parts(ctx, ops, n, resident);
     size_t bounds[MAX_H2D_PARTS + 1] = {0};
     if (parts > 1) {  // ranges that came out empty (tiny n) are dropped
         pick_bounds(ctx, n, parts, bounds, resident);

@@ -32,7 +32,10 @@ hs = torch.from_numpy(scalars).pin_memory()
 growths = [int(x) for x in os.environ.get("GROWTH", "0").split(",")]
 shareds = [int(x) for x in os.environ.get("SHARED", "1").split(",")]
 tapers = [int(x) for x in os.environ.get("TAPER", "0").split(",")]
-for sh, p, gr, tp in [(sh, p, gr, tp) for sh in shareds for p in parts for gr in growths for tp in tapers]:
+windows = [int(x) for x in os.environ.get("WINDOW", "0").split(",")]
+for sh, p, gr, tp, wb in [(sh, p, gr, tp, wb) for wb in windows for sh in shareds for p in parts for gr in growths
+                          for tp in tapers]:
+    m.set_option("window_bits", wb)
     m.set_option("h2d_shared_buckets", sh)
     m.set_option("h2d_taper", tp)
     m.set_option("h2d_parts", p)
@@ -43,4 +46,4 @@ for sh, p, gr, tp in [(sh, p, gr, tp) for sh in shareds for p in parts for gr in
         got = m.multi_exp_host_ptr(gid, hb.data_ptr(), hs.data_ptr(), n)
         best = min(best, m.timer_stop())
     ok = bool(np.array_equal(m.batch_to_special(gid, got.reshape(1, -1))[0], want))
-    print(f"shared={sh} h2d_parts={p} growth={gr} taper={tp}: e2e {best:.2f} ms = {n / best / 1e3:.1f} M points/s  same={ok}", flush=True)
+    print(f"window_bits={wb} shared={sh} h2d_parts={p} growth={gr} taper={tp}: e2e {best:.2f} ms = {n / best / 1e3:.1f} M points/s  same={ok}", flush=True)
