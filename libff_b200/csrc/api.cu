@@ -259,9 +259,10 @@ bool run_msm(Ctx &ctx, const GroupOps *ops, const void *d_aff, const uint8_t *d_
 // buckets in the merging accumulation), so the best count grows like the square root of the
 // call's length.  Measured per field class (profiles/e2e_ranges_r02d.log): the 8-limb prime field
 // gains from 2^19 points on; the merging accumulation of the wider fields is a slower kernel than
-// their plain one (the 24-limb field's is not the shared-memory slot kernel), so they take fewer
-// ranges and bw6_761 none.
-size_t pick_parts(const Ctx &ctx, const GroupOps *ops, size_t n, bool scalars_only) {
+// their plain one, so they take fewer ranges; bw6_761 takes none: at its digit sizes a range
+// leaves one or two items per bucket, and a slot-kernel variant that merges into live buckets
+// measured no better than the register one (2^19: 1 range 35.5 ms, 2 ranges 41.1).
+size_t pick_parts(const Ctx &ctx, const GroupOps *ops, size_t n, bool scalars_only, bool pageable) {
     if (scalars_only && ctx.opt_h2d_parts == 0) {
         // a quarter of the bytes: few ranges, so that the buckets stay dense in every range
         return n < ((size_t)1 << 21) ? 1 : 4;
@@ -269,9 +270,9 @@ size_t pick_parts(const Ctx &ctx, const GroupOps *ops, size_t n, bool scalars_on
     if (ctx.opt_h2d_parts > 0) return std::min<size_t>((size_t)ctx.opt_h2d_parts, std::max<size_t>(n, 1));
     const bool prime8 = ops->affine_bytes == 64;                           // alt_bn128 G1
     const bool prime24 = ops->affine_bytes == 192 && ops->scalar_bytes == 48;  // bw6_761
-    if (prime24) return 1;
     if (!ctx.opt_h2d_shared_buckets) return n < ((size_t)1 << 21) ? 1 : n < ((size_t)1 << 23) ? 3 : 5;
-    if (prime8) {
+    if (prime24) return 1;
+    if (prime8 && !pageable) {  // pageable sources are bound by the host-side staging, not by the pipeline's ends
         if (n < ((size_t)1 << 19)) return 1;
         if (n < ((size_t)1 << 20)) return 2;
         if (n < ((size_t)1 << 22)) return 4;
@@ -279,10 +280,10 @@ size_t pick_parts(const Ctx &ctx, const GroupOps *ops, size_t n, bool scalars_on
         if (n < ((size_t)1 << 25)) return 12;
         return 16;
     }
-    if (n < ((size_t)1 << 20)) return 1;
+    if (n < ((size_t)1 << (prime8 ? 21 : 20))) return 1;
     if (n < ((size_t)1 << 22)) return 2;
     if (n < ((size_t)1 << 23)) return 3;
-    return 6;
+    return prime8 ? 12 : 6;
 }
 
 // Range boundaries of a pipelined call: sizes grow geometrically (x h2d_growth %, default 1.3),
@@ -507,7 +508,7 @@ bool msm_host_on(Ctx &ctx, const GroupOps *ops, const void *bases, const void *d
     }
     if (!ctx.reserve(SL_SCALARS, n * sb, &d_sc)) return false;
     if (!ctx.reserve(SL_OUT, gb, &d_out)) return false;
-    size_t parts = pick_parts(ctx, ops, n, resident);
+    size_t parts = pick_parts(ctx, ops, n, resident, !resident && !is_pinned(bases));
     size_t bounds[MAX_H2D_PARTS + 1] = {0};
     if (parts > 1) {  // ranges that came out empty (tiny n) are dropped
         pick_bounds(ctx, n, parts, bounds, resident);
