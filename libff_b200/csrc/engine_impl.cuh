@@ -359,8 +359,12 @@ bool msm_impl(Ctx &ctx, const void *d_aff, const uint8_t *d_inf, const void *d_s
     // --- the reduction's scratch (sizes do not depend on the data)
     const uint32_t V = pre ? (B >= 4096 ? 16u : 1u) : 1u;
     const uint32_t Br = B / V;
+    // buckets per thread of the bucket reduction: 16, more only beyond 2^18 threads.  (While one
+    // CTA per window walked the chunk totals the limit was 2^16 threads, K = 128 at 2^24 points;
+    // with the window totals spread over a cluster, K = 32 is faster there: bucket reduction
+    // 3.82 -> 3.04 ms, window totals + Horner 0.87 -> 1.13, profiles/sweep_reduce_cluster_r02b.log)
     uint32_t K = 16;
-    while ((M / K) > 65536 && K < 128) K <<= 1;
+    while ((M / K) > 262144 && K < 128) K <<= 1;
     if (ctx.opt_reduce_chunk > 0) K = 1u << std::min(ctx.opt_reduce_chunk, 12);
     K = std::min(K, Br);
     const uint32_t nchunks = Br / K;
