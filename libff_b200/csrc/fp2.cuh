@@ -196,11 +196,18 @@ struct AccumRolled<Bw6761FqParams> {
 // AccumRolled: bls12_377 Fq2 rolled 43.4 -> 42.1 ms at 2^20 (accumulation 31.2 -> 29.9)
 #define B200_ACCUM_EXT12_POLICY 12
 #endif
+#ifndef B200_ACCUM_PRIME12_POLICY
+// 12-limb prime fields call their products in the accumulation too, now that operands travel by
+// value: the kernel shrinks to a third and no longer misses the instruction cache (bls12_377 G1
+// 2^22: accumulation 22.85 -> 22.21 ms; bls12_381 G1 unchanged at 23.7)
+#define B200_ACCUM_PRIME12_POLICY 12
+#endif
 template <class F>
 using AccumField = typename Rebind<F, (BaseLimbs<F>::EXT && BaseLimbs<F>::N >= 12
                                            ? (AccumRolled<typename F::Params>::value ? -12 : B200_ACCUM_EXT12_POLICY)
                                        : (!BaseLimbs<F>::EXT && AccumRolled<typename F::Params>::value)
                                            ? -BaseLimbs<F>::N
+                                       : (!BaseLimbs<F>::EXT && BaseLimbs<F>::N == 12) ? B200_ACCUM_PRIME12_POLICY
                                            : B200_CALL_MIN_LIMBS)>::type;
 
 }  // namespace b200msm
