@@ -152,12 +152,11 @@ struct BaseLimbs<Fp2<P, NR, X>> {
 #define B200_TAIL_CALL_MIN_LIMBS 12
 #endif
 #ifndef B200_TAIL_ROLLED_MIN_LIMBS
-// prime fields from this many limbs inline the ROLLED product instead: faster again than the call
-// for the 24-limb field (bw6_761 2^19: 34.8 -> 33.8 ms).  For 12-limb fields the rolled product
-// won while called products took their operands through local memory; with operands by value the
-// call is faster again (profiles/policy_sweep_r02b.log: tail kernels of bls12_377 G1 2^22
-// 4.68 -> 4.25 ms, bls12_381 G1 3.42 -> 3.26 ms).
-#define B200_TAIL_ROLLED_MIN_LIMBS 24
+// prime fields from this many limbs inline the ROLLED product instead.  That won (r01) while
+// called products took their operands through local memory; with operands by value the call is
+// faster for both wide classes (profiles/policy_sweep_r02b.log: tail kernels of bls12_377 G1 2^22
+// 4.68 -> 4.25 ms, bw6_761 G1 2^19 7.41 -> 6.94 ms), so no field rolls its tail products now.
+#define B200_TAIL_ROLLED_MIN_LIMBS 99
 #endif
 template <class F>
 using TailField = typename Rebind<F, ((!BaseLimbs<F>::EXT && BaseLimbs<F>::N >= B200_TAIL_ROLLED_MIN_LIMBS)
