@@ -164,15 +164,17 @@ using TailField = typename Rebind<F, ((!BaseLimbs<F>::EXT && BaseLimbs<F>::N >= 
                                       : BaseLimbs<F>::N >= B200_CALL_MIN_LIMBS      ? B200_CALL_MIN_LIMBS
                                       : BaseLimbs<F>::N >= B200_TAIL_CALL_MIN_LIMBS ? B200_TAIL_CALL_MIN_LIMBS
                                                                                     : B200_CALL_MIN_LIMBS)>::type;
-// The accumulation kernel inlines the products of 12-limb prime fields (calls cost 28.5 -> 37.8 ms
-// there) but calls them for the 12-limb quadratic extensions (38.3 -> 33.6 ms: three base-field
-// products per product no longer fit the instruction cache).
-// ... and rolls them (Fp::mul_rolled) where measured faster.  r01 rolled bls12_377 Fq because its
-// unrolled kernel looked instruction-fetch bound (2^22: accumulation 28.9 -> 25.9 ms) while the
-// equally wide bls12_381 Fq ran at 85 % of the pipe unrolled.  The real cause was the lowering of
-// the reduction for moduli = 1 mod 2^32 (fp.cuh, ModTab): with p and INV read from constant
-// memory the unrolled product wins for bls12_377 as well (2^22: rolled 24.3, unrolled 22.9 ms;
-// Fq2 at 2^20: 27.0 -> 21.6 ms), so both 12-limb fields are unrolled now.
+// Product policy of the ACCUMULATION kernels, per field class -- every entry measured, and
+// re-measured in r02 after out-of-line routines took their operands by value (before that a call
+// moved its operands through local memory, which is what made inlined and rolled forms win in r01):
+//   8-limb prime fields        unrolled inline
+//   12-limb prime fields       called (B200_ACCUM_PRIME12_POLICY); r01 rolled bls12_377 Fq because
+//                              its unrolled kernel ran at 75 % where bls12_381's ran at 85 %: the
+//                              cause was the reduction's lowering for moduli = 1 mod 2^32 (fp.cuh,
+//                              ModTab), not instruction fetch
+//   24-limb prime field        the shared-memory slot kernel (msm_kernels.cuh); AccumRolled only
+//                              selects the product of its register fallback / merging variant
+//   quadratic extensions       Fq2 product called, lazy reduction inside (mul_lazy above)
 template <class P>
 struct AccumRolled {
     static constexpr bool value = false;
@@ -184,15 +186,15 @@ template <>
 struct AccumRolled<Bls12377FqParams> {
     static constexpr bool value = B200_ACCUM_ROLLED_377 != 0;
 };
-// bw6_761 Fq (24 limbs): the rolled inline product also beats the call, whose operands travel
-// through the stack (2^19: accumulation 30.5 -> 25.5 ms, stack frame 1792 -> 688 bytes).
+// bw6_761 Fq (24 limbs), register kernels only: rolled inline (a by-value call of two 24-limb
+// operands still goes through the stack: 2^19 accumulation 30.5 -> 25.5 ms in r01)
 template <>
 struct AccumRolled<Bw6761FqParams> {
     static constexpr bool value = true;
 };
 #ifndef B200_ACCUM_EXT12_POLICY
-// 12-limb quadratic extensions call the base-field product (12) unless the modulus is marked
-// AccumRolled: bls12_377 Fq2 rolled 43.4 -> 42.1 ms at 2^20 (accumulation 31.2 -> 29.9)
+// base-field products of the 12-limb quadratic extensions outside the lazy product (squarings,
+// inversions): called
 #define B200_ACCUM_EXT12_POLICY 12
 #endif
 #ifndef B200_ACCUM_PRIME12_POLICY
